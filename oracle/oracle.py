@@ -1,0 +1,215 @@
+"""ctypes front end of the C oracle (oracle/libudp_oracle.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and the cpu_baseline
+leg of bench.py.  The product package never imports this module.
+
+All functions are batched over persons with plain Python loops around the per-person C
+restatement; arrays are numpy, layouts follow the reference.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(_build.build())
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _cs(center, scale):
+    """center/scale [N,2] of one dtype (float32 or float64) -> contiguous arrays + flag."""
+    center = np.ascontiguousarray(center)
+    scale = np.ascontiguousarray(scale)
+    f64 = center.dtype == np.float64
+    dt = np.float64 if f64 else np.float32
+    return center.astype(dt, copy=False), scale.astype(dt, copy=False), int(f64)
+
+
+def warp_matrices(rot_deg, center, scale, W, H):
+    """a1: [N,2,3] float32.  deep_hrnet/lib/dataset/JointsDataset.py:29-49 called as :226."""
+    center, scale, f64 = _cs(center, scale)
+    N = center.shape[0]
+    rot = np.broadcast_to(np.asarray(rot_deg, np.float64), (N,))
+    M = np.zeros((N, 2, 3), np.float32)
+    L = lib()
+    for i in range(N):
+        L.udp_o_warp_matrix(C.c_double(float(rot[i])), _p(center[i]), _p(scale[i]), f64,
+                            int(W), int(H), _p(M[i]))
+    return M
+
+
+def rotate_points(joints_xy, rot_deg, center, scale, W, H, do_clip=False):
+    """a3: joints_xy [N,K,2] float64 -> [N,K,2] float64.  JointsDataset.py:51-73."""
+    center, scale, f64 = _cs(center, scale)
+    pts = np.ascontiguousarray(joints_xy, np.float64)
+    N, K = pts.shape[:2]
+    rot = np.broadcast_to(np.asarray(rot_deg, np.float64), (N,))
+    out = np.zeros_like(pts)
+    L = lib()
+    for i in range(N):
+        L.udp_o_rotate_points(_p(pts[i]), K, 2, C.c_double(float(rot[i])), _p(center[i]),
+                              _p(scale[i]), f64, int(W), int(H), int(do_clip), _p(out[i]), 2)
+    return out
+
+
+def warp_affine_u8(src, M, W, H):
+    """a2: src uint8 [Hs,Ws,3], M float32 [2,3] -> uint8 [H,W,3] (cv2.warpAffine,
+    WARP_INVERSE_MAP|INTER_LINEAR, constant-0 border; JointsDataset.py:227)."""
+    src = np.ascontiguousarray(src, np.uint8)
+    M = np.ascontiguousarray(M, np.float32)
+    dst = np.empty((H, W, 3), np.uint8)
+    lib().udp_o_warp_affine_u8(_p(src), src.shape[0], src.shape[1], src.strides[0], _p(M),
+                               _p(dst), int(W), int(H))
+    return dst
+
+
+def _jw(joints_weight, K):
+    if joints_weight is None:
+        return None, None
+    jw = np.ascontiguousarray(np.asarray(joints_weight, np.float32).reshape(K))
+    return jw, _p(jw)
+
+
+def encode_gaussian(joints, joints_vis, W, H, w, h, sigma, joints_weight=None):
+    """a5: joints, joints_vis [N,K,3] float64 -> target [N,K,h,w] f32, target_weight [N,K,1] f32."""
+    joints = np.ascontiguousarray(joints, np.float64)
+    vis = np.ascontiguousarray(joints_vis, np.float64)
+    N, K = joints.shape[:2]
+    tgt = np.empty((N, K, h, w), np.float32)
+    tw = np.empty((N, K, 1), np.float32)
+    jw, jwp = _jw(joints_weight, K)
+    L = lib()
+    for i in range(N):
+        L.udp_o_encode_gaussian(_p(joints[i]), _p(vis[i]), K, int(W), int(H), int(w), int(h),
+                                C.c_double(sigma), jwp, _p(tgt[i]), _p(tw[i]))
+    return tgt, tw
+
+
+def encode_offset(joints, joints_vis, W, H, w, h, kpd, joints_weight=None):
+    """a6: -> target [N,3K,h,w] f32, target_weight [N,K,1] f32."""
+    joints = np.ascontiguousarray(joints, np.float64)
+    vis = np.ascontiguousarray(joints_vis, np.float64)
+    N, K = joints.shape[:2]
+    tgt = np.empty((N, 3 * K, h, w), np.float32)
+    tw = np.empty((N, K, 1), np.float32)
+    jw, jwp = _jw(joints_weight, K)
+    L = lib()
+    for i in range(N):
+        L.udp_o_encode_offset(_p(joints[i]), _p(vis[i]), K, int(W), int(H), int(w), int(h),
+                              C.c_double(kpd), jwp, _p(tgt[i]), _p(tw[i]))
+    return tgt, tw
+
+
+RSN_SIGMAS = (2.6, 2.0, 1.7, 1.4105, 1.1105)  # RSN/dataset/JointsDataset.py:19-25, kernels 15,11,9,7,5
+
+
+def encode_rsn(joints, valid, W, H, w, h, sigmas=RSN_SIGMAS):
+    """a7: joints [N,K,>=2] float64 (crop coords), valid [N,K] -> labels [N,S,K,h,w] f32."""
+    joints = np.ascontiguousarray(joints, np.float64)
+    valid = np.ascontiguousarray(valid, np.float32).reshape(joints.shape[0], -1)
+    N, K, js = joints.shape
+    sig = np.ascontiguousarray(sigmas, np.float64)
+    S = sig.shape[0]
+    out = np.empty((N, S, K, h, w), np.float32)
+    L = lib()
+    for i in range(N):
+        L.udp_o_encode_rsn(_p(joints[i]), js, _p(valid[i]), K, int(W), int(H), int(w), int(h),
+                           _p(sig), S, _p(out[i]))
+    return out
+
+
+def rsn_transform_joints(joints, vis, rot_deg, center, scale, W, H):
+    """a3': returns (joints [N,K,3] with x,y mapped where vis>0, vis [N,K,3] culled, Minv [N,2,3])."""
+    joints = np.array(joints, np.float64, copy=True)
+    vis = np.array(vis, np.float64, copy=True)
+    center = np.ascontiguousarray(center, np.float32)
+    scale = np.ascontiguousarray(scale, np.float32)
+    N, K = joints.shape[:2]
+    rot = np.broadcast_to(np.asarray(rot_deg, np.float64), (N,))
+    Minv = np.zeros((N, 2, 3), np.float32)
+    L = lib()
+    for i in range(N):
+        L.udp_o_rsn_warp_matrix_inverse(C.c_double(float(rot[i])), _p(center[i]), _p(scale[i]),
+                                        int(W), int(H), _p(Minv[i]))
+        L.udp_o_rsn_transform_joints(_p(joints[i]), joints.shape[2], _p(vis[i]), vis.shape[2], K,
+                                     _p(Minv[i]), int(W), int(H))
+    return joints, vis, Minv
+
+
+def gaussian_blur(a, n):
+    """cv2.GaussianBlur(a, (n,n), 0) for float32 [h,w], n in {7,15}."""
+    a = np.ascontiguousarray(a, np.float32)
+    out = np.empty_like(a)
+    lib().udp_o_gaussian_blur(_p(a), _p(out), a.shape[0], a.shape[1], int(n))
+    return out
+
+
+def flip_perm(K, pairs):
+    perm = np.arange(K, dtype=np.int32)
+    for a, b in pairs:
+        perm[a], perm[b] = b, a
+    return perm
+
+
+def flip_average(out, flipped, pairs, triplets=False):
+    """a9-a11: (out + flip_back(flipped)) * 0.5, [N,C,h,w] float32."""
+    out = np.ascontiguousarray(out, np.float32)
+    flipped = np.ascontiguousarray(flipped, np.float32)
+    N, Cc, h, w = out.shape
+    K = Cc // 3 if triplets else Cc
+    perm = flip_perm(K, pairs)
+    avg = np.empty_like(out)
+    L = lib()
+    for i in range(N):
+        L.udp_o_flip_average(_p(out[i]), _p(flipped[i]), _p(perm), K, h, w, int(triplets), _p(avg[i]))
+    return avg
+
+
+def decode_gaussian(hm, center, scale, post_process=True, pre_div=0.0, want_blurred=False):
+    """a12-a14,a16: hm [N,K,h,w] f32 -> dict(preds f64 [N,K,2], maxvals f32 [N,K,1],
+    preds_in f64 [N,K,2], idx int32 [N,K][, blurred])."""
+    hm = np.ascontiguousarray(hm, np.float32)
+    center, scale, f64 = _cs(center, scale)
+    N, K, h, w = hm.shape
+    preds = np.empty((N, K, 2), np.float64)
+    pin = np.empty((N, K, 2), np.float64)
+    mv = np.empty((N, K, 1), np.float32)
+    idx = np.empty((N, K), np.int32)
+    bl = np.empty_like(hm) if want_blurred else None
+    L = lib()
+    for i in range(N):
+        L.udp_o_decode_gaussian(_p(hm[i]), K, w, h, _p(center[i]), _p(scale[i]), f64,
+                                C.c_float(pre_div), int(post_process), _p(preds[i]), _p(mv[i]),
+                                _p(pin[i]), _p(idx[i]), _p(bl[i]) if want_blurred else None)
+    r = dict(preds=preds, maxvals=mv, preds_in=pin, idx=idx)
+    if want_blurred:
+        r["blurred"] = bl
+    return r
+
+
+def decode_offset(out, center, scale, kpd):
+    """a15,a16: out [N,3K,h,w] f32 -> dict as decode_gaussian (values are float32-exact)."""
+    out = np.ascontiguousarray(out, np.float32)
+    center, scale, f64 = _cs(center, scale)
+    N, C3, h, w = out.shape
+    K = C3 // 3
+    preds = np.empty((N, K, 2), np.float64)
+    pin = np.empty((N, K, 2), np.float64)
+    mv = np.empty((N, K, 1), np.float32)
+    idx = np.empty((N, K), np.int32)
+    L = lib()
+    for i in range(N):
+        L.udp_o_decode_offset(_p(out[i]), K, w, h, C.c_double(kpd), _p(center[i]), _p(scale[i]),
+                              f64, _p(preds[i]), _p(mv[i]), _p(pin[i]), _p(idx[i]))
+    return dict(preds=preds, maxvals=mv, preds_in=pin, idx=idx)

@@ -1,0 +1,131 @@
+"""Deterministic synthetic workloads for the codec.
+
+Host-side numpy generators shared by tests/, tests/golden/make_golden.py and bench.py so
+that the oracle, the reference and the CUDA path all see identical inputs.  Nothing here is
+on the product path.  seed convention: 1000 * cfg_id + trial.
+"""
+import numpy as np
+
+SRC_W, SRC_H = 640, 480
+
+
+def boxes(cfg, N, rng, rotate=False):
+    """Person boxes in a 640x480 source image.  Returns center [N,2], scale [N,2] (cfg.cs_dtype,
+    scale = box/200*1.25 as lib/dataset/coco.py:223-227) and rot [N] float64 degrees."""
+    W, H = cfg.image_size
+    bh = rng.uniform(0.25, 1.1, N) * SRC_H
+    bw = bh * W / H
+    c = rng.uniform(0.1, 0.9, (N, 2)) * np.array([SRC_W, SRC_H])
+    s = np.stack([bw, bh], 1) / 200.0 * 1.25
+    dt = np.dtype(cfg.cs_dtype)
+    if rotate:
+        rf = cfg.rot_factor
+        r = np.clip(rng.standard_normal(N) * rf, -2 * rf, 2 * rf)  # JointsDataset.py:217-218
+        r = np.where(rng.uniform(size=N) <= 0.6, r, 0.0)
+    else:
+        r = np.zeros(N)
+    return c.astype(dt), s.astype(dt), r.astype(np.float64)
+
+
+def source_images(P, rng, h=SRC_H, w=SRC_W):
+    """uint8 [P,h,w,3]: iid noise blended 50/50 with a smooth gradient."""
+    noise = rng.integers(0, 256, (P, h, w, 3)).astype(np.float32)
+    gy, gx = np.mgrid[0:h, 0:w].astype(np.float32)
+    grad = np.stack([gx / (w - 1) * 255, gy / (h - 1) * 255, (gx + gy) / (w + h - 2) * 255], -1)
+    return np.clip(0.5 * noise + 0.5 * grad[None], 0, 255).astype(np.uint8)
+
+
+def joints(cfg, N, rng, rsn=False):
+    """joints [N,K,3] float64 in crop coordinates (about 17% outside), vis [N,K,3] float64."""
+    W, H = cfg.image_size
+    K = cfg.num_joints
+    j = np.zeros((N, K, 3))
+    j[..., 0] = rng.uniform(-0.1, 1.1, (N, K)) * (W - 1)
+    j[..., 1] = rng.uniform(-0.1, 1.1, (N, K)) * (H - 1)
+    if rsn:
+        v = rng.integers(0, 3, (N, K)).astype(np.float64)
+    else:
+        v = (rng.uniform(size=(N, K)) < 0.8).astype(np.float64)
+    vis = np.zeros((N, K, 3))
+    vis[..., 0] = v
+    vis[..., 1] = v
+    return j, vis
+
+
+def _flip_of(maps, cfg):
+    """What a model would emit for the mirrored input: x-mirrored, pair-swapped
+    (and x-offset negated in offset mode) -- the inverse of flip_back*."""
+    K = cfg.num_joints
+    perm = np.arange(K)
+    for a, b in cfg.flip_pairs:
+        perm[a], perm[b] = b, a
+    if cfg.target_type == "offset":
+        N, C3, h, w = maps.shape
+        m = maps.reshape(N, K, 3, h, w)[:, perm][..., ::-1].copy()
+        m[:, :, 1] = -m[:, :, 1]
+        return m.reshape(N, C3, h, w)
+    return maps[:, perm][..., ::-1].copy()
+
+
+def heatmaps(cfg, N, rng, flip=True):
+    """Realistic decode inputs.  Returns (out, flipped or None), float32 [N,C,h,w]."""
+    w, h = cfg.heatmap_size
+    K = cfg.num_joints
+    mu = np.stack([rng.uniform(-2, w + 1, (N, K)), rng.uniform(-2, h + 1, (N, K))], -1)
+    amp = rng.uniform(0.2, 1.0, (N, K))
+    xs = np.arange(w)[None, None, None, :]
+    ys = np.arange(h)[None, None, :, None]
+    d2 = (xs - mu[..., 0, None, None]) ** 2 + (ys - mu[..., 1, None, None]) ** 2
+    if cfg.target_type == "offset":
+        cls = amp[..., None, None] * np.exp(-d2 / (2 * 2.0 ** 2))
+        keep = (d2 / cfg.kpd ** 2) <= 1
+        ox = np.where(keep, (mu[..., 0, None, None] - xs) / cfg.kpd, 0.0)
+        oy = np.where(keep, (mu[..., 1, None, None] - ys) / cfg.kpd, 0.0)
+        clean = np.stack([cls, ox, oy], 2).reshape(N, 3 * K, h, w)
+
+        def noisy():
+            nz = np.empty((N, K, 3, h, w))
+            nz[:, :, 0] = rng.uniform(-0.02, 0.02, (N, K, h, w))
+            nz[:, :, 1:] = rng.standard_normal((N, K, 2, h, w)) * 0.05
+            return nz.reshape(N, 3 * K, h, w)
+    else:
+        sig = float(cfg.sigma)
+        clean = amp[..., None, None] * np.exp(-d2 / (2 * sig ** 2))
+
+        def noisy():
+            return rng.uniform(-0.02, 0.02, (N, K, h, w))
+    mul = 255.0 if cfg.pre_div else 1.0
+    out = ((clean + noisy()) * mul).astype(np.float32)
+    if not flip:
+        return out, None
+    fl = (_flip_of(clean, cfg) + noisy()) * mul
+    return out, fl.astype(np.float32)
+
+
+def adversarial_heatmaps(cfg, rng):
+    """Small adversarial parity set for the gaussian decoder: float32 [M,K,h,w].
+    Rows: U(0,1) noise, N(0,1) noise, all-negative, exact ties, border/corner peaks,
+    single non-zero pixel.  (Constant maps -> NaN in the reference, tested separately.)"""
+    w, h = cfg.heatmap_size
+    K = cfg.num_joints
+    rows = []
+    rows.append(rng.uniform(0, 1, (K, h, w)))
+    rows.append(rng.standard_normal((K, h, w)))
+    rows.append(-rng.uniform(0.1, 1, (K, h, w)))
+    t = rng.uniform(0, 0.5, (K, h, w))
+    for k in range(K):
+        p = rng.integers(0, h * w, 2)
+        t[k].reshape(-1)[p] = 0.75
+    rows.append(t)
+    b = rng.uniform(0, 0.05, (K, h, w))
+    spots = [(0, 0), (0, w - 1), (h - 1, 0), (h - 1, w - 1), (0, w // 2), (h - 1, w // 2),
+             (h // 2, 0), (h // 2, w - 1)]
+    for k in range(K):
+        y, x = spots[k % len(spots)]
+        b[k, y, x] = 1.0
+    rows.append(b)
+    z = np.zeros((K, h, w))
+    for k in range(K):
+        z[k, rng.integers(0, h), rng.integers(0, w)] = 0.9
+    rows.append(z)
+    return np.stack(rows).astype(np.float32)
