@@ -1,0 +1,137 @@
+/*
+ * udp_codec.h -- C ABI of the B200 (sm_100a) UDP heatmap codec.
+ *
+ * This is the drop-in boundary for the codec hot path of realphongha/UDP-Pose.  The
+ * reference has no FFI of its own: the path sits behind plain Python functions
+ * (SURVEY.md 8b).  Each entry point below names the reference function(s) it replaces,
+ * paths relative to the reference root.  INTEGRATION.md shows the ctypes binding a
+ * maintainer adds on the reference side.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the comment says HOST; row-major, dense;
+ *  - `stream` is a cudaStream_t (NULL = default stream); calls are asynchronous;
+ *  - return value: 0 on success, otherwise a cudaError_t (> 0) or UDP_EINVAL (< 0);
+ *    no exceptions cross the ABI, nothing is allocated, nothing is synchronised;
+ *  - `cs_f64`: dtype of the center/scale arrays -- 1 = float64 (MPII records,
+ *    lib/dataset/mpii.py:55-56), 0 = float32 (COCO records, lib/dataset/coco.py:223-227).
+ *    The reference's arithmetic depends on that dtype (numpy promotion), so it is part of
+ *    the contract;
+ *  - N = number of person instances, K = joints, (W,H) network input, (w,h) heatmap.
+ */
+#ifndef UDP_CODEC_H
+#define UDP_CODEC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UDP_EINVAL (-1)
+#define UDP_MAX_SIGMAS 8
+
+/* Library version (major*10000 + minor*100 + patch) and the SM architecture compiled in. */
+int udp_codec_version(void);
+int udp_codec_sm_arch(void);
+
+/* a1  get_warpmatrix(r, c*2.0, image_size-1.0, s)
+ *     deep_hrnet/lib/dataset/JointsDataset.py:29-49, call :226 (RSN twin RSN/dataset/JointsDataset.py:49-69).
+ *     rot_deg [N] float64 or NULL (= 0).  M_out [N,2,3] float32 (dst->src, for WARP_INVERSE_MAP). */
+int udp_warp_matrices(const void *center, const void *scale, int cs_f64, const double *rot_deg,
+                      int W, int H, float *M_out, int N, void *stream);
+
+/* a2  cv2.warpAffine(img u8 HWC3, M, (W,H), flags=WARP_INVERSE_MAP|INTER_LINEAR), border 0
+ *     call sites JointsDataset.py:227, RSN/dataset/JointsDataset.py:197-198.
+ *     src_ptrs [N] device array of device pointers (one image per person, may repeat);
+ *     src_h/src_w/src_stride [N] int32 (stride in bytes).  dst [N,H,W,3] uint8.
+ *     Bit-exact with OpenCV's fixed-point path (Q10 coordinates, Q5 fractions, Q15 weights). */
+int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
+                       const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H,
+                       int N, void *stream);
+
+/* a3  rotate_points(joints[:, 0:2], r, c, image_size, s, do_clip)  JointsDataset.py:51-73, call :228.
+ *     joints [N,K,jstride] float64 (x,y at 0,1), out [N,K,ostride] float64; may alias. */
+int udp_rotate_points(const double *joints, int jstride, const double *rot_deg, const void *center,
+                      const void *scale, int cs_f64, int W, int H, int do_clip, double *out,
+                      int ostride, int K, int N, void *stream);
+
+/* a3' RSN: get_warpmatrix_inverse + affine_transform + visibility cull
+ *     RSN/dataset/JointsDataset.py:27-47, :203-211; RSN/lib/utils/transforms.py:38-41.
+ *     joints [N,K,jstride] f64 and vis [N,K,vstride] f64 are updated IN PLACE; center/scale f32.
+ *     Minv_out [N,2,3] float32 (nullable). */
+int udp_rsn_transform_joints(double *joints, int jstride, double *vis, int vstride,
+                             const double *rot_deg, const float *center, const float *scale,
+                             int W, int H, float *Minv_out, int K, int N, void *stream);
+
+/* a4  fliplr_joints(joints, joints_vis, width, matched_parts)  deep_hrnet/lib/utils/transforms.py:50-64
+ *     (mul_vis = 1: returns joints*joints_vis) and RSN flip_joints RSN/lib/utils/transforms.py:70-79
+ *     (mul_vis = 0).  joints, joints_vis [N,K,3] f64; width [N] int32 (image width per person);
+ *     outputs must not alias the inputs. */
+int udp_fliplr_joints(const double *joints, const double *joints_vis, const int32_t *flip_perm,
+                      const int32_t *width, int K, int N, int mul_vis, double *joints_out,
+                      double *vis_out, void *stream);
+
+/* a16 transform_preds(coords, center, scale, [w,h])  deep_hrnet/lib/core/inference.py:20-27
+ *     (= utils/transforms.py:67-74, RSN prm test.py:29-39).  coords [N,K,2] float64 or float32
+ *     (coords_f64); out [N,K,2] float64 (the reference returns np.zeros(coords.shape)). */
+int udp_transform_preds(const void *coords, int coords_f64, const void *center, const void *scale,
+                        int cs_f64, int w, int h, double *out, int K, int N, void *stream);
+
+/* a5  JointsDataset.generate_target, TARGET_TYPE 'gaussian'  JointsDataset.py:291-348,382-383.
+ *     joints, joints_vis [N,K,3] float64; joints_weight [K] float32 or NULL
+ *     (LOSS.USE_DIFFERENT_JOINTS_WEIGHT).  target [N,K,h,w] f32, target_weight [N,K,1] f32. */
+int udp_encode_gaussian(const double *joints, const double *joints_vis, const float *joints_weight,
+                        int K, int W, int H, int w, int h, double sigma, float *target,
+                        float *target_weight, int N, void *stream);
+
+/* a6  generate_target, TARGET_TYPE 'offset' (UDPv1)  JointsDataset.py:349-381.
+ *     target [N,3K,h,w] f32, channel order (j,cls),(j,xoff),(j,yoff). */
+int udp_encode_offset(const double *joints, const double *joints_vis, const float *joints_weight,
+                      int K, int W, int H, int w, int h, double kpd, float *target,
+                      float *target_weight, int N, void *stream);
+
+/* a7  RSN generate_heatmap for S kernel sizes  RSN/dataset/JointsDataset.py:276-291, :214-220.
+ *     joints [N,K,jstride] f64 (crop coords), valid [N,K] f32 (drawn iff >= 1),
+ *     sigmas: HOST pointer to S <= UDP_MAX_SIGMAS doubles.  labels [N,S,K,h,w] f32. */
+int udp_encode_rsn(const double *joints, int jstride, const float *valid, int K, int W, int H,
+                   int w, int h, const double *sigmas, int S, float *labels, int N, void *stream);
+
+/* a9/a10/a11  flip_back / flip_back_offset (+ average)
+ *     deep_hrnet/lib/utils/transforms.py:15-47 (RSN/lib/utils/transforms.py:59-67),
+ *     lib/core/function.py:171.
+ *     flipped [N,C,h,w]; flip_perm [K] int32 (partner joint, identity where unpaired);
+ *     triplets = 1: C = 3K and the x-offset channel is negated.  out == NULL: dst = flip_back(flipped);
+ *     else dst = (out + flip_back(flipped)) * 0.5.  dst must not alias flipped. */
+int udp_flip_back(const float *out, const float *flipped, const int32_t *flip_perm, int K, int w,
+                  int h, int triplets, float *dst, int N, void *stream);
+
+/* a12/a13/a14/a16/a17  get_final_preds, TARGET_TYPE 'gaussian', with the flip test fused in
+ *     deep_hrnet/lib/core/inference.py:30-58 (get_max_preds), :60-145 (post), :149-155,176-186,
+ *     :20-27 (transform_preds); flip: utils/transforms.py:15-29 + core/function.py:171;
+ *     RSN prm: RSN/exps/RSN18.coco.e1.se.36x8x132000_prm/test.py:183-196 (pre_div = 255).
+ *     hm [N,K,h,w] f32; hm_flipped same shape or NULL; flip_perm [K] (ignored when NULL flipped).
+ *     center/scale [N,2] or NULL (NULL: coordinates stay in heatmap space = get_max_preds / post).
+ *     pre_div: 0 = none, else maps are divided by it first.  post_process = TEST.POST_PROCESS.
+ *     preds, preds_in [N,K,2]: float64 when post_process else float32 (the reference's dtypes);
+ *     maxvals [N,K,1] f32; argmax_idx [N,K] int32 (nullable); packed [N,K,3] f32 x,y,maxval
+ *     (nullable; the all_preds layout of function.py:208-209, used for the multi-GPU gather);
+ *     blurred [N,K,h,w] f32 (nullable; the maps post() writes back into its input, :80). */
+int udp_decode_gaussian(const float *hm, const float *hm_flipped, const int32_t *flip_perm,
+                        const void *center, const void *scale, int cs_f64, float pre_div,
+                        int post_process, int K, int w, int h, void *preds, float *maxvals,
+                        void *preds_in, int32_t *argmax_idx, float *packed, float *blurred, int N,
+                        void *stream);
+
+/* a10/a11/a15/a16  get_final_preds, TARGET_TYPE 'offset' (UDPv1 voting), flip test fused in
+ *     inference.py:156-174,176-186; flip: utils/transforms.py:31-47 + function.py:171.
+ *     out [N,3K,h,w] f32; out_flipped or NULL.  preds, preds_in [N,K,2] float32;
+ *     maxvals = maxima of the 15x15-blurred classification maps; argmax_idx their argmax. */
+int udp_decode_offset(const float *out, const float *out_flipped, const int32_t *flip_perm,
+                      double kpd, const void *center, const void *scale, int cs_f64, int K, int w,
+                      int h, float *preds, float *maxvals, float *preds_in, int32_t *argmax_idx,
+                      float *packed, int N, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UDP_CODEC_H */

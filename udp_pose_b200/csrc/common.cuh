@@ -1,0 +1,55 @@
+// common.cuh -- shared helpers for the sm_100a UDP codec kernels.
+//
+// Compile flags that are part of the numerical contract (see __graft_entry__.build()):
+//   -fmad=false   : no implicit FMA contraction; fused ops appear only where fmaf()/fma() is
+//                   written, mirroring OpenCV's FMA order and numpy's
+//                   separately rounded multiplies and adds;
+//   no -use_fast_math: IEEE division / sqrt, denormals kept.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/udp_codec.h"
+
+#define UDP_LAUNCH_CHECK()                     \
+    do {                                       \
+        cudaError_t e__ = cudaGetLastError();  \
+        if (e__ != cudaSuccess) return (int)e__; \
+    } while (0)
+
+namespace udp {
+
+constexpr double kPi = 3.141592653589793;  // math.pi
+
+// 16-byte streaming store: outputs are written once and never re-read by this library.
+__device__ __forceinline__ void st_stream_f4(float *p, float4 v) { __stcs(reinterpret_cast<float4 *>(p), v); }
+// 16-byte read-once load (keeps L1 for the gathers that do reuse lines).
+__device__ __forceinline__ float4 ld_stream_f4(const float *p) { return __ldcs(reinterpret_cast<const float4 *>(p)); }
+
+// center/scale loader honouring the caller's dtype.
+struct CS {
+    double c0, c1;   // center as double (exact widening when float32)
+    double st0, st1; // scale*200 rounded in the caller's dtype, widened
+    float c0f, c1f, st0f, st1f;
+};
+
+__device__ __forceinline__ CS load_cs(const void *center, const void *scale, int cs_f64, int n)
+{
+    CS r;
+    if (cs_f64) {
+        const double *c = reinterpret_cast<const double *>(center) + 2 * (size_t)n;
+        const double *s = reinterpret_cast<const double *>(scale) + 2 * (size_t)n;
+        r.c0 = c[0]; r.c1 = c[1];
+        r.st0 = __dmul_rn(s[0], 200.0); r.st1 = __dmul_rn(s[1], 200.0);
+        r.c0f = r.c1f = r.st0f = r.st1f = 0.f;
+    } else {
+        const float *c = reinterpret_cast<const float *>(center) + 2 * (size_t)n;
+        const float *s = reinterpret_cast<const float *>(scale) + 2 * (size_t)n;
+        r.c0f = c[0]; r.c1f = c[1];
+        r.st0f = __fmul_rn(s[0], 200.0f); r.st1f = __fmul_rn(s[1], 200.0f);
+        r.c0 = r.c0f; r.c1 = r.c1f; r.st0 = r.st0f; r.st1 = r.st1f;
+    }
+    return r;
+}
+
+}  // namespace udp

@@ -1,0 +1,138 @@
+// crop.cu -- the UDP person crop: bit-exact restatement of OpenCV's fixed-point bilinear
+// warpAffine (u8, 3 channels, WARP_INVERSE_MAP | INTER_LINEAR, constant-0 border).
+//
+// Reference call sites: deep_hrnet/lib/dataset/JointsDataset.py:227,
+// RSN/dataset/JointsDataset.py:197-198.  OpenCV arithmetic:
+//   X = (rint((M01*y+M02)*1024) + 16 + rint(M00*x*1024)) >> 5      (Q5 source coordinate)
+//   sx = X>>5, fx = X&31 ; likewise Y ; weights (32-fy)(32-fx)*32 ... sum to 2^15
+//   dst = (sum w*p + 2^14) >> 15
+// The four weights factor exactly (integers, no intermediate rounding):
+//   sum w*p = 32 * [ (32-fy)*((32-fx)*p00 + fx*p01) + fy*((32-fx)*p10 + fx*p11) ]
+// so dst = (S + 512) >> 10 with S the bracket -- one dp4a per source row pair.
+//
+// Layout: one CTA = one person x ROWS output rows.  The per-column deltas
+// rint(M00*x*1024), rint(M10*x*1024) and the per-row bases are float64 and are computed
+// once per CTA into shared memory; the per-pixel work is integer only.  The finished
+// ROWS x W x 3 byte tile is staged in shared memory and leaves as 16-byte streaming stores.
+#include "common.cuh"
+
+namespace udp {
+
+constexpr int CROP_ROWS = 16;
+constexpr int CROP_THREADS = 256;
+
+__device__ __forceinline__ uint32_t ldg_u8(const uint8_t *p) { return (uint32_t)__ldg(p); }
+
+__global__ void __launch_bounds__(CROP_THREADS)
+warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
+                      const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    int32_t *ad = reinterpret_cast<int32_t *>(smem_raw);  // [W]
+    int32_t *bd = ad + W;                                 // [W]
+    int32_t *X0 = bd + W;                                 // [CROP_ROWS]
+    int32_t *Y0 = X0 + CROP_ROWS;                         // [CROP_ROWS]
+    uint8_t *tile = reinterpret_cast<uint8_t *>(Y0 + CROP_ROWS);  // [CROP_ROWS][W*3], 16B aligned (W even)
+
+    const int n = blockIdx.y;
+    const int y_base = blockIdx.x * CROP_ROWS;
+    const int rows = min(CROP_ROWS, H - y_base);
+    const float *m = M + 6 * (size_t)n;
+    const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
+
+    for (int x = threadIdx.x; x < W; x += CROP_THREADS) {
+        ad[x] = __double2int_rn(__dmul_rn(__dmul_rn(m00, (double)x), 1024.0));
+        bd[x] = __double2int_rn(__dmul_rn(__dmul_rn(m10, (double)x), 1024.0));
+    }
+    if (threadIdx.x < rows) {
+        double y = (double)(y_base + threadIdx.x);
+        X0[threadIdx.x] = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m01, y), m02), 1024.0)) + 16;
+        Y0[threadIdx.x] = __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m11, y), m12), 1024.0)) + 16;
+    }
+    __syncthreads();
+
+    const uint8_t *src = src_ptrs[n];
+    const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
+    const int row_bytes = W * 3;
+
+    for (int p = threadIdx.x; p < rows * W; p += CROP_THREADS) {
+        int r = p / W, x = p - r * W;
+        int X = (X0[r] + ad[x]) >> 5, Y = (Y0[r] + bd[x]) >> 5;
+        int sx = X >> 5, sy = Y >> 5;
+        uint32_t fx = X & 31, fy = Y & 31;
+        // dp4a weight vectors: row 0 taps in bytes 0,1 ; row 1 taps in bytes 2,3
+        uint32_t wx = (32u - fx) | (fx << 8);
+        uint32_t a0, a1, a2;  // [p00 p01 p10 p11] per channel
+        if (sx >= 0 && sy >= 0 && sx + 1 < sw && sy + 1 < sh) {
+            const uint8_t *q0 = src + (size_t)sy * ss + sx * 3;
+            const uint8_t *q1 = q0 + ss;
+            uint32_t r0 = ldg_u8(q0), g0 = ldg_u8(q0 + 1), b0 = ldg_u8(q0 + 2);
+            uint32_t r1 = ldg_u8(q0 + 3), g1 = ldg_u8(q0 + 4), b1 = ldg_u8(q0 + 5);
+            uint32_t r2 = ldg_u8(q1), g2 = ldg_u8(q1 + 1), b2 = ldg_u8(q1 + 2);
+            uint32_t r3 = ldg_u8(q1 + 3), g3 = ldg_u8(q1 + 4), b3 = ldg_u8(q1 + 5);
+            a0 = r0 | (r1 << 8) | (r2 << 16) | (r3 << 24);
+            a1 = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+            a2 = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+        } else {
+            bool x0 = sx >= 0 && sx < sw, x1 = sx + 1 >= 0 && sx + 1 < sw;
+            bool y0 = sy >= 0 && sy < sh, y1 = sy + 1 >= 0 && sy + 1 < sh;
+            a0 = a1 = a2 = 0;
+            if (y0 && x0) { const uint8_t *q = src + (size_t)sy * ss + sx * 3;
+                a0 |= ldg_u8(q); a1 |= ldg_u8(q + 1); a2 |= ldg_u8(q + 2); }
+            if (y0 && x1) { const uint8_t *q = src + (size_t)sy * ss + (sx + 1) * 3;
+                a0 |= ldg_u8(q) << 8; a1 |= ldg_u8(q + 1) << 8; a2 |= ldg_u8(q + 2) << 8; }
+            if (y1 && x0) { const uint8_t *q = src + (size_t)(sy + 1) * ss + sx * 3;
+                a0 |= ldg_u8(q) << 16; a1 |= ldg_u8(q + 1) << 16; a2 |= ldg_u8(q + 2) << 16; }
+            if (y1 && x1) { const uint8_t *q = src + (size_t)(sy + 1) * ss + (sx + 1) * 3;
+                a0 |= ldg_u8(q) << 24; a1 |= ldg_u8(q + 1) << 24; a2 |= ldg_u8(q + 2) << 24; }
+        }
+        uint32_t wy0 = 32u - fy;
+        uint32_t h0, h1, S;
+        uint8_t *o = tile + r * row_bytes + x * 3;
+        h0 = __dp4a(a0, wx, 0u); h1 = __dp4a(a0, wx << 16, 0u);
+        S = wy0 * h0 + fy * h1; o[0] = (uint8_t)((S + 512u) >> 10);
+        h0 = __dp4a(a1, wx, 0u); h1 = __dp4a(a1, wx << 16, 0u);
+        S = wy0 * h0 + fy * h1; o[1] = (uint8_t)((S + 512u) >> 10);
+        h0 = __dp4a(a2, wx, 0u); h1 = __dp4a(a2, wx << 16, 0u);
+        S = wy0 * h0 + fy * h1; o[2] = (uint8_t)((S + 512u) >> 10);
+    }
+    __syncthreads();
+
+    // tile -> global, 16-byte streaming stores (tile rows are contiguous in dst as well).
+    uint8_t *out = dst + ((size_t)n * H + y_base) * row_bytes;
+    const int total = rows * row_bytes;
+    if ((row_bytes & 15) == 0) {
+        const int4 *t4 = reinterpret_cast<const int4 *>(tile);
+        int4 *o4 = reinterpret_cast<int4 *>(out);
+        for (int i = threadIdx.x; i < total / 16; i += CROP_THREADS) __stcs(o4 + i, t4[i]);
+    } else {
+        for (int i = threadIdx.x; i < total; i += CROP_THREADS) out[i] = tile[i];
+    }
+}
+
+}  // namespace udp
+
+extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h,
+                                  const int32_t *src_w, const int32_t *src_stride, const float *M,
+                                  uint8_t *dst, int W, int H, int N, void *stream)
+{
+    if (N < 0 || W < 1 || H < 1 || (W & 1)) return UDP_EINVAL;
+    if (N == 0) return 0;
+    if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst) return UDP_EINVAL;
+    size_t smem = sizeof(int32_t) * (2 * (size_t)W + 2 * udp::CROP_ROWS) + (size_t)udp::CROP_ROWS * W * 3;
+    if (smem > 200 * 1024) return UDP_EINVAL;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(udp::warp_affine_u8_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+    }
+    for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
+        int nn = N - n0 < 65535 ? N - n0 : 65535;
+        dim3 grid((H + udp::CROP_ROWS - 1) / udp::CROP_ROWS, nn);
+        udp::warp_affine_u8_kernel<<<grid, udp::CROP_THREADS, smem, (cudaStream_t)stream>>>(
+            src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
+            dst + (size_t)n0 * H * W * 3, W, H);
+        UDP_LAUNCH_CHECK();
+    }
+    return 0;
+}

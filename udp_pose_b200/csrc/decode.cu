@@ -1,0 +1,282 @@
+// decode.cu -- flip_back(+average) and the fused 'gaussian' decoder:
+//   flip-back + average  ->  raw argmax  ->  7x7 blur + renormalise  ->  clip/log  ->
+//   Taylor (DARK-style) refinement  ->  UDP inverse affine,
+// one CTA per (person, joint) map, the map read from HBM exactly once.
+//
+// Reference (paths relative to the reference root):
+//   flip_back / flip_back_offset   deep_hrnet/lib/utils/transforms.py:15-47
+//   average                        deep_hrnet/lib/core/function.py:171
+//   get_max_preds                  deep_hrnet/lib/core/inference.py:30-58
+//   post                           deep_hrnet/lib/core/inference.py:60-145
+//   get_final_preds (gaussian)     deep_hrnet/lib/core/inference.py:149-155,176-186
+//   transform_preds                deep_hrnet/lib/core/inference.py:20-27
+//   RSN prm glue (/255.0)          RSN/exps/RSN18.coco.e1.se.36x8x132000_prm/test.py:183-196
+#include "blur.cuh"
+
+namespace udp {
+
+// ---------------------------------------------------------------------------------------
+// a9/a10/a11 as a standalone elementwise kernel (the decoders fuse it; this one serves the
+// reference's own call sites, which want the flipped-back tensor itself).
+// ---------------------------------------------------------------------------------------
+__global__ void flip_back_kernel(const float *__restrict__ out, const float *__restrict__ fl,
+                                 const int32_t *__restrict__ perm, int K, int w, int h,
+                                 int triplets, float *__restrict__ dst, long long total4)
+{
+    const int w4 = w >> 2, per = triplets ? 3 : 1;
+    const int per_map = w4 * h;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long map = i / per_map;  // index into [N, K*per]
+        const int j = (int)(i - map * per_map);
+        const int y = j / w4, x = (j - y * w4) << 2;
+        const int C = K * per;
+        const long long n = map / C;
+        const int c = (int)(map - n * C);
+        const int joint = c / per, t = c - joint * per;
+        const long long smap = n * C + (long long)perm[joint] * per + t;
+        float4 f = ld_stream_f4(fl + smap * (long long)(h * w) + (size_t)y * w + (w - 4 - x));
+        const float sg = (triplets && t == 1) ? -1.0f : 1.0f;
+        float4 r = make_float4(sg * f.w, sg * f.z, sg * f.y, sg * f.x);
+        if (out) {
+            const float4 a = ld_stream_f4(out + i * 4);
+            r.x = __fmul_rn(__fadd_rn(a.x, r.x), 0.5f); r.y = __fmul_rn(__fadd_rn(a.y, r.y), 0.5f);
+            r.z = __fmul_rn(__fadd_rn(a.z, r.z), 0.5f); r.w = __fmul_rn(__fadd_rn(a.w, r.w), 0.5f);
+        }
+        st_stream_f4(dst + i * 4, r);
+    }
+}
+
+// np.clip(x, 0.001, 50) then np.log, float32 (inference.py:81-82).  The log is the correctly
+// rounded float32 logarithm (evaluated in float64, rounded once).
+__device__ __forceinline__ double clip_log(float v)
+{
+    if (v == v) v = v < 0.001f ? 0.001f : (v > 50.0f ? 50.0f : v);
+    return (double)(float)log((double)v);
+}
+
+// 2x2 inverse as np.linalg.inv computes it (LAPACK gesv: LU, partial pivoting); an exactly
+// zero pivot is the LinAlgError branch -> zero matrix (inference.py:126-132).
+__device__ __forceinline__ void inv2x2(double a, double b, double c, double d, double *inv)
+{
+    double r00 = a, r01 = b, r10 = c, r11 = d;
+    double e00 = 1, e01 = 0, e10 = 0, e11 = 1;
+    if (fabs(c) > fabs(a)) { r00 = c; r01 = d; r10 = a; r11 = b; e00 = 0; e01 = 1; e10 = 1; e11 = 0; }
+    inv[0] = inv[1] = inv[2] = inv[3] = 0.0;
+    if (r00 == 0.0) return;
+    const double l = __ddiv_rn(r10, r00);
+    const double u11 = __dsub_rn(r11, __dmul_rn(l, r01));
+    if (u11 == 0.0) return;
+    {
+        const double y1 = __dsub_rn(e10, __dmul_rn(l, e00));
+        const double x1 = __ddiv_rn(y1, u11);
+        inv[0] = __ddiv_rn(__dsub_rn(e00, __dmul_rn(r01, x1)), r00);
+        inv[2] = x1;
+    }
+    {
+        const double y1 = __dsub_rn(e11, __dmul_rn(l, e01));
+        const double x1 = __ddiv_rn(y1, u11);
+        inv[1] = __ddiv_rn(__dsub_rn(e01, __dmul_rn(r01, x1)), r00);
+        inv[3] = x1;
+    }
+}
+
+struct DecodeGaussArgs {
+    const float *hm, *hm_flipped;
+    const int32_t *flip_perm;
+    const void *center, *scale;
+    int cs_f64;
+    float pre_div;
+    int K, w, h;
+    void *preds;
+    float *maxvals;
+    void *preds_in;
+    int32_t *argmax_idx;
+    float *packed;
+    float *blurred;
+};
+
+template <bool POST>
+__global__ void decode_gaussian_kernel(DecodeGaussArgs p)
+{
+    constexpr int R = 3, L = 8;
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float red_v[32];
+    __shared__ int red_i[32];
+    __shared__ float red_mn[32], red_mx[32];
+    __shared__ int red_nan[32];
+    __shared__ float nb[9];
+
+    const int w = p.w, h = p.h, hw = h * w;
+    const long long map = blockIdx.x;  // n*K + k
+    const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
+    float *A = smem;
+    float *T = A + (size_t)h * BlurGeom<R>::stride_a(w);
+
+    const float *src = p.hm + map * (long long)hw;
+    const float *fl = p.hm_flipped ? p.hm_flipped + ((long long)n * p.K + p.flip_perm[k]) * (long long)hw : nullptr;
+
+    float bv;
+    int bi;
+    load_tile<R>(src, fl, 1.0f, p.pre_div, w, h, A, bv, bi);
+    __syncthreads();
+    if (POST) fill_pads<R>(A, w, h);
+    block_argmax(bv, bi, red_v, red_i);  // contains the __syncthreads that publishes the pads
+
+    // get_max_preds: x = idx % w, y = floor(idx / w); coords zeroed unless maxval > 0
+    const bool mask = bv > 0.0f;
+    const int ix = mask ? bi % w : 0, iy = mask ? bi / w : 0;
+    double cx = (double)ix, cy = (double)iy;
+
+    if (POST) {
+        row_pass<R>(A, T, w, h);
+        __syncthreads();
+        float mn = INFINITY, mx = -INFINITY;
+        int has_nan = 0;
+        float *B = A;  // A is dead after the row pass; reused for the blurred map if requested
+        const bool keep = p.blurred != nullptr;
+        col_pass<R, L>(T, w, h, [&](int y, int x, float4 s) {
+            mn = fminf(fminf(mn, fminf(s.x, s.y)), fminf(s.z, s.w));
+            mx = fmaxf(fmaxf(mx, fmaxf(s.x, s.y)), fmaxf(s.z, s.w));
+            has_nan |= (s.x != s.x) | (s.y != s.y) | (s.z != s.z) | (s.w != s.w);
+            const int dy = y - iy + 1;
+            if (dy >= 0 && dy <= 2) {
+                const float vv[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int dx = x + c - ix + 1;
+                    if (dx >= 0 && dx <= 2) nb[dy * 3 + dx] = vv[c];
+                }
+            }
+            if (keep) *reinterpret_cast<float4 *>(B + y * w + x) = s;
+        });
+        // block min / max (np.min / np.max propagate NaN)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            has_nan |= __shfl_xor_sync(0xffffffffu, has_nan, o);
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+        if (lane == 0) { red_mn[warp] = mn; red_mx[warp] = mx; red_nan[warp] = has_nan; }
+        __syncthreads();
+        mn = red_mn[0]; mx = red_mx[0]; has_nan = red_nan[0];
+        for (int q = 1; q < nwarps; ++q) {
+            mn = fminf(mn, red_mn[q]); mx = fmaxf(mx, red_mx[q]); has_nan |= red_nan[q];
+        }
+        if (has_nan) mn = mx = __int_as_float(0x7fc00000);
+        const float range = __fsub_rn(mx, mn);
+        const float maxori = bv;  // np.max of the raw map (:74)
+
+        if (keep) {  // post() writes the renormalised blurred map back (:79-80)
+            float *dst = p.blurred + map * (long long)hw;
+            for (int j = threadIdx.x; j < hw / 4; j += blockDim.x) {
+                float4 s = *reinterpret_cast<const float4 *>(B + j * 4);
+                s.x = __fmul_rn(__fdiv_rn(__fsub_rn(s.x, mn), range), maxori);
+                s.y = __fmul_rn(__fdiv_rn(__fsub_rn(s.y, mn), range), maxori);
+                s.z = __fmul_rn(__fdiv_rn(__fsub_rn(s.z, mn), range), maxori);
+                s.w = __fmul_rn(__fdiv_rn(__fsub_rn(s.w, mn), range), maxori);
+                st_stream_f4(dst + j * 4, s);
+            }
+        }
+
+        if (threadIdx.x < 32) {
+            // lanes 0..6: one stencil tap each (edge-replicated, :83-109)
+            const int tdy[7] = {0, 0, 0, 1, -1, 1, -1};
+            const int tdx[7] = {0, 1, -1, 0, 0, 1, -1};
+            double tap = 0.0;
+            if (lane < 7) {
+                const int yy = min(max(iy + tdy[lane], 0), h - 1), xx = min(max(ix + tdx[lane], 0), w - 1);
+                const float raw = nb[(yy - iy + 1) * 3 + (xx - ix + 1)];
+                const float nv = __fmul_rn(__fdiv_rn(__fsub_rn(raw, mn), range), maxori);  // :79
+                tap = clip_log(nv);
+            }
+            const double I = __shfl_sync(0xffffffffu, tap, 0), Ix1 = __shfl_sync(0xffffffffu, tap, 1);
+            const double Ix1_ = __shfl_sync(0xffffffffu, tap, 2), Iy1 = __shfl_sync(0xffffffffu, tap, 3);
+            const double Iy1_ = __shfl_sync(0xffffffffu, tap, 4), Ix1y1 = __shfl_sync(0xffffffffu, tap, 5);
+            const double Ix1_y1_ = __shfl_sync(0xffffffffu, tap, 6);
+            const double dx = __dmul_rn(0.5, __dsub_rn(Ix1, Ix1_));
+            const double dy = __dmul_rn(0.5, __dsub_rn(Iy1, Iy1_));
+            const double dxx = __dadd_rn(__dsub_rn(Ix1, __dmul_rn(2.0, I)), Ix1_);
+            const double dyy = __dadd_rn(__dsub_rn(Iy1, __dmul_rn(2.0, I)), Iy1_);
+            double t = __dsub_rn(Ix1y1, Ix1);
+            t = __dsub_rn(t, Iy1); t = __dadd_rn(t, I); t = __dadd_rn(t, I);
+            t = __dsub_rn(t, Ix1_); t = __dsub_rn(t, Iy1_); t = __dadd_rn(t, Ix1_y1_);
+            const double dxy = __dmul_rn(0.5, t);
+            double inv[4];
+            inv2x2(dxx, dxy, dxy, dyy, inv);
+            cx = __dsub_rn((double)ix, __dadd_rn(__dmul_rn(inv[0], dx), __dmul_rn(inv[1], dy)));
+            cy = __dsub_rn((double)iy, __dadd_rn(__dmul_rn(inv[2], dx), __dmul_rn(inv[3], dy)));
+        }
+    }
+
+    if (threadIdx.x == 0) {
+        double pin_x, pin_y, ox = cx, oy = cy;
+        if (POST) {  // :178-179 on a float64 array
+            pin_x = __dmul_rn(__ddiv_rn(cx, w - 1.0), 4 * w - 1.0);
+            pin_y = __dmul_rn(__ddiv_rn(cy, h - 1.0), 4 * h - 1.0);
+        } else {     // float32 array / python float
+            pin_x = (double)__fmul_rn(__fdiv_rn((float)cx, (float)(w - 1.0)), (float)(4 * w - 1.0));
+            pin_y = (double)__fmul_rn(__fdiv_rn((float)cy, (float)(h - 1.0)), (float)(4 * h - 1.0));
+        }
+        if (p.center) {
+            const CS cs = load_cs(p.center, p.scale, p.cs_f64, n);
+            transform_pred(cx, cy, cs, p.cs_f64, POST, w, h, ox, oy);
+        }
+        if (POST) {
+            double *pr = reinterpret_cast<double *>(p.preds) + map * 2;
+            pr[0] = ox; pr[1] = oy;
+            if (p.preds_in) { double *q = reinterpret_cast<double *>(p.preds_in) + map * 2; q[0] = pin_x; q[1] = pin_y; }
+        } else {
+            float *pr = reinterpret_cast<float *>(p.preds) + map * 2;
+            pr[0] = (float)ox; pr[1] = (float)oy;
+            if (p.preds_in) { float *q = reinterpret_cast<float *>(p.preds_in) + map * 2; q[0] = (float)pin_x; q[1] = (float)pin_y; }
+        }
+        p.maxvals[map] = bv;
+        if (p.argmax_idx) p.argmax_idx[map] = bi;
+        if (p.packed) { float *q = p.packed + map * 3; q[0] = (float)ox; q[1] = (float)oy; q[2] = bv; }
+    }
+}
+
+}  // namespace udp
+
+extern "C" int udp_flip_back(const float *out, const float *flipped, const int32_t *flip_perm,
+                             int K, int w, int h, int triplets, float *dst, int N, void *stream)
+{
+    if (N < 0 || K < 1 || w < 4 || (w & 3) || h < 1) return UDP_EINVAL;
+    if (N == 0) return 0;
+    if (!flipped || !flip_perm || !dst || dst == flipped) return UDP_EINVAL;
+    long long total4 = (long long)N * K * (triplets ? 3 : 1) * h * (w >> 2);
+    long long blocks = (total4 + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    udp::flip_back_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        out, flipped, flip_perm, K, w, h, triplets, dst, total4);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
+                                   const int32_t *flip_perm, const void *center, const void *scale,
+                                   int cs_f64, float pre_div, int post_process, int K, int w, int h,
+                                   void *preds, float *maxvals, void *preds_in, int32_t *argmax_idx,
+                                   float *packed, float *blurred, int N, void *stream)
+{
+    if (N < 0 || K < 1 || w < 8 || (w & 3) || h < 8) return UDP_EINVAL;
+    if (N == 0) return 0;
+    if (!hm || !preds || !maxvals || (hm_flipped && !flip_perm) || ((center == nullptr) != (scale == nullptr)))
+        return UDP_EINVAL;
+    if (blurred && !post_process) return UDP_EINVAL;
+    udp::DecodeGaussArgs a{hm, hm_flipped, flip_perm, center, scale, cs_f64, pre_div, K, w, h,
+                           preds, maxvals, preds_in, argmax_idx, packed, blurred};
+    size_t smem = udp::BlurGeom<3>::smem_floats(w, h) * sizeof(float);
+    if (smem > 200 * 1024) return UDP_EINVAL;
+    auto kern = post_process ? udp::decode_gaussian_kernel<true> : udp::decode_gaussian_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    const int threads = (h * w <= 4096) ? 128 : 256;
+    long long maps = (long long)N * K;
+    if (maps > 0x7fffffffLL) return UDP_EINVAL;
+    kern<<<(unsigned)maps, threads, smem, (cudaStream_t)stream>>>(a);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,307 @@
+"""Batched device API: CUDA tensors in, CUDA tensors out, one kernel launch per call.
+
+This is the fast path that bench.py times.  Every function maps 1:1 onto a C-ABI entry point
+of include/udp_codec.h; torch is used only for device memory and streams.  All launches go
+to torch's current CUDA stream.  Nothing here touches the CPU oracle; a missing
+libudp_codec.so raises (udp_pose_b200._lib.load).
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_F64 = torch.float64
+_F32 = torch.float32
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _dev(t, dtype=None):
+    """Contiguous CUDA tensor of the wanted dtype (numpy arrays are uploaded)."""
+    if isinstance(t, np.ndarray):
+        t = torch.from_numpy(np.ascontiguousarray(t))
+    if not t.is_cuda:
+        t = t.cuda(non_blocking=True)
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.contiguous()
+
+
+def _cs(center, scale):
+    """center/scale keep their dtype (float32 or float64): it selects the arithmetic."""
+    center = _dev(center)
+    scale = _dev(scale)
+    if center.dtype not in (_F32, _F64):
+        center = center.to(_F64)
+    scale = scale.to(center.dtype)
+    return center, scale, int(center.dtype == _F64)
+
+
+_perm_cache = {}
+
+
+def flip_perm(K, pairs, device):
+    """int32 [K] partner-joint table from a flip_pairs list (cached per device)."""
+    key = (K, tuple(map(tuple, pairs)), str(device))
+    if key not in _perm_cache:
+        perm = list(range(K))
+        for a, b in pairs:
+            perm[a], perm[b] = b, a
+        _perm_cache[key] = torch.tensor(perm, dtype=torch.int32, device=device)
+    return _perm_cache[key]
+
+
+# ---------------------------------------------------------------------------- crop side
+def warp_matrices(center, scale, rot_deg, image_size):
+    """a1 get_warpmatrix(r, c*2.0, image_size-1.0, s), batched -> float32 [N,2,3]."""
+    center, scale, f64 = _cs(center, scale)
+    N = center.shape[0]
+    rot = _dev(rot_deg, _F64) if rot_deg is not None else None
+    M = torch.empty((N, 2, 3), dtype=_F32, device=center.device)
+    _lib.call("udp_warp_matrices", _ptr(center), _ptr(scale), f64, _ptr(rot), int(image_size[0]),
+              int(image_size[1]), _ptr(M), N, _stream())
+    return M
+
+
+class SourceImages:
+    """Device-resident source images for the crop: per-person pointer/shape tables.
+
+    images: list of uint8 CUDA tensors [Hs,Ws,3] (HWC, last two dims dense), or one uint8
+    tensor [P,Hs,Ws,3]; index: which image each person uses (len N)."""
+
+    def __init__(self, images, index):
+        if isinstance(images, torch.Tensor) and images.dim() == 4:
+            images = [images[i] for i in range(images.shape[0])]
+        self.images = [_dev(im, torch.uint8) for im in images]
+        for im in self.images:
+            assert im.dim() == 3 and im.shape[2] == 3 and im.stride(2) == 1 and im.stride(1) == 3
+        index = np.asarray(index.cpu() if isinstance(index, torch.Tensor) else index, dtype=np.int64)
+        dev = self.images[0].device
+        ptrs = np.array([self.images[i].data_ptr() for i in index], dtype=np.int64)
+        hs = np.array([self.images[i].shape[0] for i in index], dtype=np.int32)
+        ws = np.array([self.images[i].shape[1] for i in index], dtype=np.int32)
+        st = np.array([self.images[i].stride(0) for i in index], dtype=np.int32)
+        self.ptrs = torch.from_numpy(ptrs).to(dev)
+        self.h = torch.from_numpy(hs).to(dev)
+        self.w = torch.from_numpy(ws).to(dev)
+        self.stride = torch.from_numpy(st).to(dev)
+        self.n = len(index)
+
+
+def crop_batch(src, M, image_size, out=None):
+    """a2 cv2.warpAffine(img, M, (W,H), WARP_INVERSE_MAP|INTER_LINEAR) for N persons.
+    src: SourceImages; M float32 [N,2,3] -> uint8 [N,H,W,3]."""
+    W, H = int(image_size[0]), int(image_size[1])
+    M = _dev(M, _F32)
+    N = M.shape[0]
+    assert src.n == N
+    if out is None:
+        out = torch.empty((N, H, W, 3), dtype=torch.uint8, device=M.device)
+    _lib.call("udp_warp_affine_u8", _ptr(src.ptrs), _ptr(src.h), _ptr(src.w), _ptr(src.stride),
+              _ptr(M), _ptr(out), W, H, N, _stream())
+    return out
+
+
+def rotate_points_batch(joints, rot_deg, center, scale, image_size, do_clip=False):
+    """a3 rotate_points on joints [N,K,>=2] float64 -> float64 [N,K,2]."""
+    joints = _dev(joints, _F64)
+    center, scale, f64 = _cs(center, scale)
+    N, K, js = joints.shape
+    rot = _dev(rot_deg, _F64) if rot_deg is not None else None
+    out = torch.empty((N, K, 2), dtype=_F64, device=joints.device)
+    _lib.call("udp_rotate_points", _ptr(joints), js, _ptr(rot), _ptr(center), _ptr(scale), f64,
+              int(image_size[0]), int(image_size[1]), int(do_clip), _ptr(out), 2, K, N, _stream())
+    return out
+
+
+def rsn_transform_joints_batch(joints, vis, rot_deg, center, scale, image_size):
+    """a3' RSN joint map + visibility cull.  Returns new (joints [N,K,3], vis [N,K,3], Minv [N,2,3])."""
+    joints = _dev(joints, _F64).clone()
+    vis = _dev(vis, _F64).clone()
+    center = _dev(center, _F32)
+    scale = _dev(scale, _F32)
+    N, K, js = joints.shape
+    rot = _dev(rot_deg, _F64) if rot_deg is not None else None
+    Minv = torch.empty((N, 2, 3), dtype=_F32, device=joints.device)
+    _lib.call("udp_rsn_transform_joints", _ptr(joints), js, _ptr(vis), vis.shape[2], _ptr(rot),
+              _ptr(center), _ptr(scale), int(image_size[0]), int(image_size[1]), _ptr(Minv), K, N,
+              _stream())
+    return joints, vis, Minv
+
+
+def fliplr_joints_batch(joints, vis, width, pairs, mul_vis=True):
+    """a4 fliplr_joints for N persons; width int or [N]."""
+    joints = _dev(joints, _F64)
+    vis = _dev(vis, _F64)
+    N, K, _ = joints.shape
+    if np.isscalar(width):
+        width = torch.full((N,), int(width), dtype=torch.int32, device=joints.device)
+    width = _dev(width, torch.int32)
+    perm = flip_perm(K, pairs, joints.device)
+    jo, vo = torch.empty_like(joints), torch.empty_like(vis)
+    _lib.call("udp_fliplr_joints", _ptr(joints), _ptr(vis), _ptr(perm), _ptr(width), K, N,
+              int(mul_vis), _ptr(jo), _ptr(vo), _stream())
+    return jo, vo
+
+
+# -------------------------------------------------------------------------- encode side
+def encode_gaussian(joints, vis, image_size, heatmap_size, sigma, joints_weight=None, out=None):
+    """a5 -> (target f32 [N,K,h,w], target_weight f32 [N,K,1])."""
+    joints, vis = _dev(joints, _F64), _dev(vis, _F64)
+    N, K, _ = joints.shape
+    (W, H), (w, h) = image_size, heatmap_size
+    tgt = out if out is not None else torch.empty((N, K, h, w), dtype=_F32, device=joints.device)
+    tw = torch.empty((N, K, 1), dtype=_F32, device=joints.device)
+    jw = _dev(joints_weight, _F32).reshape(-1) if joints_weight is not None else None
+    _lib.call("udp_encode_gaussian", _ptr(joints), _ptr(vis), _ptr(jw), K, int(W), int(H), int(w),
+              int(h), float(sigma), _ptr(tgt), _ptr(tw), N, _stream())
+    return tgt, tw
+
+
+def encode_offset(joints, vis, image_size, heatmap_size, kpd, joints_weight=None, out=None):
+    """a6 -> (target f32 [N,3K,h,w], target_weight f32 [N,K,1])."""
+    joints, vis = _dev(joints, _F64), _dev(vis, _F64)
+    N, K, _ = joints.shape
+    (W, H), (w, h) = image_size, heatmap_size
+    tgt = out if out is not None else torch.empty((N, 3 * K, h, w), dtype=_F32, device=joints.device)
+    tw = torch.empty((N, K, 1), dtype=_F32, device=joints.device)
+    jw = _dev(joints_weight, _F32).reshape(-1) if joints_weight is not None else None
+    _lib.call("udp_encode_offset", _ptr(joints), _ptr(vis), _ptr(jw), K, int(W), int(H), int(w),
+              int(h), float(kpd), _ptr(tgt), _ptr(tw), N, _stream())
+    return tgt, tw
+
+
+def encode_rsn(joints, valid, image_size, heatmap_size, sigmas, out=None):
+    """a7 -> labels f32 [N,S,K,h,w].  joints [N,K,>=2] f64 crop coords, valid [N,K]."""
+    joints = _dev(joints, _F64)
+    N, K, js = joints.shape
+    valid = _dev(valid, _F32).reshape(N, K)
+    (W, H), (w, h) = image_size, heatmap_size
+    S = len(sigmas)
+    sig = (C.c_double * S)(*[float(s) for s in sigmas])
+    lab = out if out is not None else torch.empty((N, S, K, h, w), dtype=_F32, device=joints.device)
+    _lib.call("udp_encode_rsn", _ptr(joints), js, _ptr(valid), K, int(W), int(H), int(w), int(h),
+              C.cast(sig, C.c_void_p), S, _ptr(lab), N, _stream())
+    return lab
+
+
+def encode_batch(cfg, joints, vis, joints_weight=None, out=None):
+    """Target encode for a CodecConfig (udp_pose_b200.configs)."""
+    if cfg.target_type == "gaussian":
+        return encode_gaussian(joints, vis, cfg.image_size, cfg.heatmap_size, cfg.sigma, joints_weight, out)
+    if cfg.target_type == "offset":
+        return encode_offset(joints, vis, cfg.image_size, cfg.heatmap_size, cfg.kpd, joints_weight, out)
+    from .configs import RSN_SIGMAS
+    v = vis[..., 0] if vis.dim() == 3 else vis
+    return encode_rsn(joints, v, cfg.image_size, cfg.heatmap_size, RSN_SIGMAS, out), None
+
+
+# -------------------------------------------------------------------------- decode side
+def flip_back(flipped, pairs, triplets=False, out=None):
+    """a9/a10 (out=None) or a9-a11 fused: (out + flip_back(flipped)) * 0.5."""
+    flipped = _dev(flipped, _F32)
+    N, Cc, h, w = flipped.shape
+    K = Cc // 3 if triplets else Cc
+    perm = flip_perm(K, pairs, flipped.device)
+    o = _dev(out, _F32) if out is not None else None
+    dst = torch.empty_like(flipped)
+    _lib.call("udp_flip_back", _ptr(o), _ptr(flipped), _ptr(perm), K, w, h, int(triplets), _ptr(dst),
+              N, _stream())
+    return dst
+
+
+def decode_gaussian(hm, center, scale, flipped=None, pairs=None, post_process=True, pre_div=0.0,
+                    want_idx=False, want_packed=False, want_blurred=False):
+    """a9,a11-a14,a16(,a17): fused flip-average + get_final_preds('gaussian').
+    center/scale None -> heatmap-space coordinates (get_max_preds / post).
+    Returns dict(preds, maxvals, preds_in[, idx, packed, blurred])."""
+    hm = _dev(hm, _F32)
+    N, K, h, w = hm.shape
+    dev = hm.device
+    fl = perm = None
+    if flipped is not None:
+        fl = _dev(flipped, _F32)
+        assert fl.shape == hm.shape
+        perm = flip_perm(K, pairs or [], dev)
+    c = s = None
+    f64 = 0
+    if center is not None:
+        c, s, f64 = _cs(center, scale)
+    dt = _F64 if post_process else _F32
+    preds = torch.empty((N, K, 2), dtype=dt, device=dev)
+    pin = torch.empty((N, K, 2), dtype=dt, device=dev)
+    mv = torch.empty((N, K, 1), dtype=_F32, device=dev)
+    idx = torch.empty((N, K), dtype=torch.int32, device=dev) if want_idx else None
+    packed = torch.empty((N, K, 3), dtype=_F32, device=dev) if want_packed else None
+    bl = torch.empty_like(hm) if want_blurred else None
+    _lib.call("udp_decode_gaussian", _ptr(hm), _ptr(fl), _ptr(perm), _ptr(c), _ptr(s), f64,
+              float(pre_div), int(bool(post_process)), K, w, h, _ptr(preds), _ptr(mv), _ptr(pin),
+              _ptr(idx), _ptr(packed), _ptr(bl), N, _stream())
+    r = dict(preds=preds, maxvals=mv, preds_in=pin)
+    if want_idx:
+        r["idx"] = idx
+    if want_packed:
+        r["packed"] = packed
+    if want_blurred:
+        r["blurred"] = bl
+    return r
+
+
+def decode_offset(out, center, scale, kpd, flipped=None, pairs=None, want_idx=False,
+                  want_packed=False):
+    """a10,a11,a15,a16: fused flip-average + get_final_preds('offset')."""
+    out = _dev(out, _F32)
+    N, C3, h, w = out.shape
+    K = C3 // 3
+    dev = out.device
+    fl = perm = None
+    if flipped is not None:
+        fl = _dev(flipped, _F32)
+        assert fl.shape == out.shape
+        perm = flip_perm(K, pairs or [], dev)
+    c = s = None
+    f64 = 0
+    if center is not None:
+        c, s, f64 = _cs(center, scale)
+    preds = torch.empty((N, K, 2), dtype=_F32, device=dev)
+    pin = torch.empty((N, K, 2), dtype=_F32, device=dev)
+    mv = torch.empty((N, K, 1), dtype=_F32, device=dev)
+    idx = torch.empty((N, K), dtype=torch.int32, device=dev) if want_idx else None
+    packed = torch.empty((N, K, 3), dtype=_F32, device=dev) if want_packed else None
+    _lib.call("udp_decode_offset", _ptr(out), _ptr(fl), _ptr(perm), float(kpd), _ptr(c), _ptr(s),
+              f64, K, w, h, _ptr(preds), _ptr(mv), _ptr(pin), _ptr(idx), _ptr(packed), N, _stream())
+    r = dict(preds=preds, maxvals=mv, preds_in=pin)
+    if want_idx:
+        r["idx"] = idx
+    if want_packed:
+        r["packed"] = packed
+    return r
+
+
+def decode_batch(cfg, out, flipped, center, scale, post_process=None, **kw):
+    """Decode for a CodecConfig; `flipped` may be None (no flip test)."""
+    if cfg.target_type == "offset":
+        return decode_offset(out, center, scale, cfg.kpd, flipped, cfg.flip_pairs, **kw)
+    pp = cfg.post_process if post_process is None else post_process
+    return decode_gaussian(out, center, scale, flipped, cfg.flip_pairs, pp, cfg.pre_div, **kw)
+
+
+def transform_preds_batch(coords, center, scale, heatmap_size):
+    """a16 transform_preds for coords [N,K,2] (float32 or float64) -> float64 [N,K,2]."""
+    coords = _dev(coords)
+    if coords.dtype not in (_F32, _F64):
+        coords = coords.to(_F64)
+    center, scale, f64 = _cs(center, scale)
+    N, K, _ = coords.shape
+    out = torch.empty((N, K, 2), dtype=_F64, device=coords.device)
+    _lib.call("udp_transform_preds", _ptr(coords), int(coords.dtype == _F64), _ptr(center),
+              _ptr(scale), f64, int(heatmap_size[0]), int(heatmap_size[1]), _ptr(out), K, N, _stream())
+    return out
