@@ -1,0 +1,231 @@
+"""GPU: the CUDA path, called through the C ABI, against (1) the committed golden vectors of
+the unmodified reference and (2) the C oracle on fresh seeded inputs, plus size-independent
+properties at larger N."""
+import numpy as np
+import pytest
+
+import parity
+from parity import same_bits
+from udp_pose_b200 import synth
+from udp_pose_b200.configs import CONFIGS, RSN_SIGMAS
+
+pytestmark = pytest.mark.gpu
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+class CudaImpl:
+    """Adapter over udp_pose_b200.device_api with the interface parity.py expects."""
+
+    def __init__(self):
+        import torch
+        from udp_pose_b200 import _lib, device_api
+        assert torch.cuda.is_available()
+        _lib.load()  # raises if libudp_codec.so is missing: no fallback
+        self.D = device_api
+        self.torch = torch
+
+    def warp_matrices(self, rot, c, s, W, H):
+        return _np(self.D.warp_matrices(c, s, np.asarray(rot, np.float64), (W, H)))
+
+    def rotate_points(self, jxy, rot, c, s, W, H):
+        return _np(self.D.rotate_points_batch(np.ascontiguousarray(jxy), np.asarray(rot, np.float64), c, s, (W, H)))
+
+    def warp_affine(self, images, index, M, W, H):
+        src = self.D.SourceImages([self.torch.from_numpy(np.ascontiguousarray(im)) for im in images], index)
+        return _np(self.D.crop_batch(src, M, (W, H)))
+
+    def encode_gaussian(self, j, v, W, H, w, h, sigma, jw=None):
+        t, tw = self.D.encode_gaussian(j, v, (W, H), (w, h), sigma, jw)
+        return _np(t), _np(tw)
+
+    def encode_offset(self, j, v, W, H, w, h, kpd, jw=None):
+        t, tw = self.D.encode_offset(j, v, (W, H), (w, h), kpd, jw)
+        return _np(t), _np(tw)
+
+    def encode_rsn(self, j, valid, W, H, w, h):
+        return _np(self.D.encode_rsn(j, np.ascontiguousarray(valid), (W, H), (w, h), RSN_SIGMAS))
+
+    def rsn_transform_joints(self, j, v, rot, c, s, W, H):
+        a, b, m = self.D.rsn_transform_joints_batch(j, v, np.asarray(rot, np.float64), c, s, (W, H))
+        return _np(a), _np(b), _np(m)
+
+    def decode(self, cfg, out, flipped, c, s, post_process=True, **kw):
+        r = self.D.decode_batch(cfg, out, flipped, c, s, post_process=post_process, want_idx=True, **kw)
+        return {k: _np(v).astype(np.float64) if k in ("preds", "preds_in") else _np(v) for k, v in r.items()}
+
+
+@pytest.fixture(scope="module")
+def impl():
+    return CudaImpl()
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return parity.OracleImpl()
+
+
+# ------------------------------------------------------------------ golden vectors
+@pytest.mark.parametrize("cid", sorted(CONFIGS))
+def test_golden_crop_side(impl, cid):
+    parity.check_crop_side(impl, cid)
+
+
+@pytest.mark.parametrize("cid", sorted(CONFIGS))
+def test_golden_encode(impl, cid):
+    parity.check_encode(impl, cid)
+
+
+@pytest.mark.parametrize("cid", sorted(CONFIGS))
+def test_golden_decode(impl, cid):
+    parity.check_decode(impl, cid)
+
+
+def test_golden_adversarial(impl):
+    parity.check_adversarial(impl)
+
+
+# ------------------------------------------------------------------ oracle, fresh seeds
+@pytest.mark.parametrize("cid", sorted(CONFIGS))
+@pytest.mark.parametrize("N", [1, 7, 32])
+def test_crop_vs_oracle(impl, orc, cid, N):
+    cfg = CONFIGS[cid]
+    W, H = cfg.image_size
+    rng = np.random.default_rng(1000 * cid + N)
+    c, s, r = synth.boxes(cfg, N, rng, rotate=True)
+    M = orc.warp_matrices(r, c, s, W, H)
+    Mg = impl.warp_matrices(r, c, s, W, H)
+    assert same_bits(M[r == 0], Mg[r == 0])
+    np.testing.assert_allclose(Mg, M, rtol=1.2e-7, atol=1e-30)
+    imgs = synth.source_images(3, rng)
+    idx = np.arange(N) % 3
+    want = orc.warp_affine(imgs, idx, M, W, H)
+    got = impl.warp_affine(imgs, idx, M, W, H)
+    assert np.array_equal(want, got)  # u8 crop bit-exact
+    K = cfg.num_joints
+    js = np.stack([rng.uniform(0, 640, (N, K)), rng.uniform(0, 480, (N, K))], -1)
+    assert np.abs(orc.rotate_points(js, r, c, s, W, H) - impl.rotate_points(js, r, c, s, W, H)).max() <= 1e-9
+
+
+@pytest.mark.parametrize("cid", sorted(CONFIGS))
+@pytest.mark.parametrize("N", [1, 7, 64])
+def test_encode_vs_oracle(impl, orc, cid, N):
+    cfg = CONFIGS[cid]
+    W, H = cfg.image_size
+    w, h = cfg.heatmap_size
+    rng = np.random.default_rng(2000 * cid + N)
+    j, v = synth.joints(cfg, N, rng, rsn=cfg.target_type == "rsn")
+    if cfg.target_type == "rsn":
+        a, b = orc.encode_rsn(j, v[..., 0], W, H, w, h), impl.encode_rsn(j, v[..., 0], W, H, w, h)
+        err = np.abs(a.astype(np.float64) - b)
+        assert (err <= np.maximum(1e-5, np.spacing(np.abs(a)))).all()
+        assert (a != b).mean() < 1e-4  # rounding ties only
+        return
+    if cfg.target_type == "gaussian":
+        (a, aw), (b, bw) = orc.encode_gaussian(j, v, W, H, w, h, cfg.sigma), impl.encode_gaussian(j, v, W, H, w, h, cfg.sigma)
+    else:
+        (a, aw), (b, bw) = orc.encode_offset(j, v, W, H, w, h, cfg.kpd), impl.encode_offset(j, v, W, H, w, h, cfg.kpd)
+        assert same_bits(a, b)  # offset target: every channel bit-exact
+    assert same_bits(aw, bw)
+    assert np.array_equal(a != 0, b != 0)
+    assert np.abs(a - b).max() <= 1e-7
+
+
+@pytest.mark.parametrize("cid", sorted(CONFIGS))
+@pytest.mark.parametrize("flip", [True, False])
+def test_decode_vs_oracle(impl, orc, cid, flip):
+    cfg = CONFIGS[cid]
+    N = 33
+    rng = np.random.default_rng(3000 * cid + flip)
+    out, fl = synth.heatmaps(cfg, N, rng, flip=flip)
+    c, s, _ = synth.boxes(cfg, N, rng)
+    a = orc.decode(cfg, out, fl, c, s)
+    b = impl.decode(cfg, out, fl, c, s)
+    assert np.array_equal(a["idx"], b["idx"])            # argmax indices bit-exact
+    assert same_bits(a["maxvals"], b["maxvals"])         # incl. the blurred maxima (offset mode)
+    assert np.abs(a["preds"] - b["preds"]).max() <= 1e-4
+    assert np.abs(a["preds_in"] - b["preds_in"]).max() <= 1e-4
+    if cfg.target_type == "offset":
+        assert same_bits(a["preds"].astype(np.float32), b["preds"].astype(np.float32))
+
+
+@pytest.mark.parametrize("cid", [1, 3, 4, 5])
+def test_blurred_writeback(impl, orc, cid):
+    """post() overwrites its input with the blurred, renormalised maps (inference.py:80)."""
+    cfg = CONFIGS[cid]
+    rng = np.random.default_rng(4000 + cid)
+    out, _ = synth.heatmaps(cfg, 5, rng, flip=False)
+    c, s, _ = synth.boxes(cfg, 5, rng)
+    want = orc.O.decode_gaussian(out, c, s, True, cfg.pre_div, want_blurred=True)["blurred"]
+    got = impl.decode(cfg, out, None, c, s, want_blurred=True)["blurred"]
+    assert same_bits(want, got)
+
+
+def test_edge_maps(impl, orc):
+    """Constant map -> NaN coords (0/0 at inference.py:79); NaN-ness must match the oracle."""
+    cfg = CONFIGS[1]
+    w, h = cfg.heatmap_size
+    hm = np.zeros((2, cfg.num_joints, h, w), np.float32)
+    hm[0] = 0.25
+    hm[1, :, 10, 10] = 1.0
+    c, s, _ = synth.boxes(cfg, 2, np.random.default_rng(5))
+    a, b = orc.decode(cfg, hm, None, c, s), impl.decode(cfg, hm, None, c, s)
+    assert np.array_equal(np.isnan(a["preds"]), np.isnan(b["preds"]))
+    assert np.isnan(b["preds"][0]).all() and not np.isnan(b["preds"][1]).any()
+    assert np.abs(a["preds"][1] - b["preds"][1]).max() <= 1e-4
+
+
+def test_empty_batch(impl):
+    cfg = CONFIGS[1]
+    w, h = cfg.heatmap_size
+    r = impl.decode(cfg, np.zeros((0, 17, h, w), np.float32), None, np.zeros((0, 2), np.float32),
+                    np.zeros((0, 2), np.float32))
+    assert r["preds"].shape == (0, 17, 2)
+    t, tw = impl.encode_gaussian(np.zeros((0, 17, 3)), np.zeros((0, 17, 3)), 192, 256, w, h, 2)
+    assert t.shape == (0, 17, h, w)
+
+
+# ------------------------------------------------------------------ properties at size
+@pytest.mark.parametrize("cid", [1, 2])
+def test_roundtrip_large(impl, cid):
+    """encode -> decode round trip at N = 4096: decoding the encoder's own target recovers
+    the joint positions (size-independent property; no oracle involved)."""
+    import torch
+    from udp_pose_b200 import device_api as D
+    cfg = CONFIGS[cid]
+    N = 4096
+    W, H = cfg.image_size
+    w, h = cfg.heatmap_size
+    rng = np.random.default_rng(77 + cid)
+    j, v = synth.joints(cfg, N, rng)
+    j[..., 0] = rng.uniform(0.1, 0.9, j.shape[:2]) * (W - 1)
+    j[..., 1] = rng.uniform(0.1, 0.9, j.shape[:2]) * (H - 1)
+    v[:] = 1.0
+    tgt, tw = D.encode_batch(cfg, j, v)
+    assert float(tw.min()) == 1.0
+    r = D.decode_batch(cfg, tgt, None, None, None)
+    hm_xy = r["preds"].double().cpu().numpy()
+    fs = np.array([(W - 1.0) / (w - 1.0), (H - 1.0) / (h - 1.0)])
+    err = np.abs(hm_xy * fs - j[..., :2])
+    tol = 0.02 if cid == 1 else 1.0  # Taylor refinement of an exact Gaussian / blurred offset vote
+    assert err.max() <= tol, err.max()
+    torch.cuda.synchronize()
+
+
+def test_flip_idempotence_large(impl):
+    """flip_back(flip_back(x)) == x and decode(x, flipped=flip(x)) == decode(x) at N = 2048."""
+    import torch
+    from udp_pose_b200 import device_api as D
+    for cid in (1, 2):
+        cfg = CONFIGS[cid]
+        trip = cfg.target_type == "offset"
+        w, h = cfg.heatmap_size
+        g = torch.Generator(device="cuda").manual_seed(cid)
+        x = torch.rand((2048, cfg.channels, h, w), device="cuda", generator=g)
+        f = D.flip_back(x, cfg.flip_pairs, trip)
+        assert torch.equal(D.flip_back(f, cfg.flip_pairs, trip), x)
+        a = D.decode_batch(cfg, x, None, None, None, want_idx=True)
+        b = D.decode_batch(cfg, x, f, None, None, want_idx=True)  # (x + x) * 0.5 == x exactly
+        assert torch.equal(a["idx"], b["idx"]) and torch.equal(a["preds"], b["preds"])
