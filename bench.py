@@ -1,0 +1,494 @@
+#!/usr/bin/env python
+"""bench.py -- UDP heatmap codec throughput on B200 (person-instances/sec, encode+decode).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): COCO HRNet-W32 256x192 UDPv1 -- per person one pass of
+  warp matrices -> 256x192 bilinear crop -> joint forward map -> classification/offset target
+  (KPD 3.5, 51x64x48) -> flip-fused offset-vote decode of a 51x64x48 network output pair.
+A step is that pass over one batch of synthetic persons per GPU (weak scaling); the persons
+are sharded contiguously over ranks and the keypoints are gathered once per step (NCCL).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG_ID = 2
+METRIC = "person_instances_per_sec_encode_decode"
+UNIT = "persons/s"
+N_IMAGES = 64
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=16384, help="persons per GPU per step")
+    ap.add_argument("--e2e-batch", type=int, default=2048, help="persons per GPU per e2e step")
+    ap.add_argument("--e2e-chunk", type=int, default=256)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--config", type=int, default=CFG_ID)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------
+# algorithmic (compulsory) bytes per person, SURVEY.md 8(d)
+# ----------------------------------------------------------------------------------------
+def _clip_poly(poly, w, h):
+    """Sutherland-Hodgman clip of a convex polygon to [0,w]x[0,h]; returns its area."""
+    def clip(pts, inside, inter):
+        out = []
+        for i in range(len(pts)):
+            a, b = pts[i], pts[(i + 1) % len(pts)]
+            ia, ib = inside(a), inside(b)
+            if ia:
+                out.append(a)
+            if ia != ib:
+                out.append(inter(a, b))
+        return out
+
+    def ix(x):
+        return lambda a, b: (x, a[1] + (b[1] - a[1]) * (x - a[0]) / (b[0] - a[0]))
+
+    def iy(y):
+        return lambda a, b: (a[0] + (b[0] - a[0]) * (y - a[1]) / (b[1] - a[1]), y)
+    for inside, inter in ((lambda p: p[0] >= 0, ix(0.0)), (lambda p: p[0] <= w, ix(float(w))),
+                          (lambda p: p[1] >= 0, iy(0.0)), (lambda p: p[1] <= h, iy(float(h)))):
+        poly = clip(poly, inside, inter)
+        if not poly:
+            return 0.0
+    a = 0.0
+    for i in range(len(poly)):
+        x0, y0 = poly[i]
+        x1, y1 = poly[(i + 1) % len(poly)]
+        a += x0 * y1 - x1 * y0
+    return abs(a) * 0.5
+
+
+def crop_src_area(center, scale, rot, src_w, src_h):
+    """Per-person area (source pixels) of the rotated box footprint clipped to the image."""
+    out = np.zeros(len(rot))
+    for i in range(len(rot)):
+        bw, bh = float(scale[i, 0]) * 200.0, float(scale[i, 1]) * 200.0
+        th = np.deg2rad(rot[i])
+        c, s = np.cos(th), np.sin(th)
+        pts = []
+        for dx, dy in ((-bw / 2, -bh / 2), (bw / 2, -bh / 2), (bw / 2, bh / 2), (-bw / 2, bh / 2)):
+            pts.append((center[i, 0] + c * dx + s * dy, center[i, 1] - s * dx + c * dy))
+        out[i] = _clip_poly(pts, src_w, src_h)
+    return out
+
+
+def algorithmic_bytes(cfg, src_area_mean):
+    """Bytes per person of each stage: every input byte once, every output byte once."""
+    K, C = cfg.num_joints, cfg.channels
+    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+    hw4 = h * w * 4
+    cs = 8 if cfg.cs_dtype == "float64" else 4
+    tgt = (5 * K if cfg.target_type == "rsn" else C) * hw4
+    b = {
+        "warp_matrices": 2 * 2 * cs + 8 + 24,
+        "rotate_points": K * 24 + 2 * 2 * cs + 8 + K * 16,
+        "crop": 3.0 * src_area_mean + W * H * 3 + 24,
+        "encode": K * 3 * 8 * 2 + tgt + K * 4,
+        # SURVEY 8(d) figure: both network outputs in full + preds/maxvals/preds_in out
+        "decode_survey": 2 * C * hw4 + K * 36,
+    }
+    if cfg.target_type == "offset":
+        # what this decoder must read: the 2K classification maps in full, plus per joint two
+        # 7x7 offset windows from each tensor (7 rows x one 32-byte sector x 2 channels x 2)
+        b["decode"] = 2 * K * hw4 + K * 2 * 2 * 7 * 32 + K * 36
+    else:
+        b["decode"] = b["decode_survey"]
+    return b
+
+
+# ----------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+# ----------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "50"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if not (t0 - 0.05 <= t <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[1]))
+                smax = float(f[2])
+            except (ValueError, IndexError):
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------
+# synthetic workload resident in HBM
+# ----------------------------------------------------------------------------------------
+def make_device_workload(cfg, B, rank, torch, D):
+    """Deterministic per-rank synthetic batch (SURVEY 8d distributions), generated outside
+    the timed region.  Heat maps are produced on the device in slices."""
+    from udp_pose_b200 import synth
+    dev = torch.device("cuda")
+    rng = np.random.default_rng(1000 * CFG_ID + rank)
+    c, s, r = synth.boxes(cfg, B, rng, rotate=True)
+    K = cfg.num_joints
+    js = np.zeros((B, K, 3))
+    js[..., 0] = c[:, None, 0] + rng.uniform(-0.6, 0.6, (B, K)) * s[:, None, 0] * 200.0
+    js[..., 1] = c[:, None, 1] + rng.uniform(-0.6, 0.6, (B, K)) * s[:, None, 1] * 200.0
+    v = (rng.uniform(size=(B, K)) < 0.8).astype(np.float64)
+    vis = np.zeros((B, K, 3))
+    vis[..., 0] = vis[..., 1] = v
+    imgs = synth.source_images(N_IMAGES, rng)
+    wl = dict(center=torch.from_numpy(c).to(dev), scale=torch.from_numpy(s).to(dev),
+              rot=torch.from_numpy(r).to(dev), joints=torch.from_numpy(js).to(dev),
+              vis=torch.from_numpy(vis).to(dev), images=torch.from_numpy(imgs).to(dev),
+              image_index=np.arange(B) % N_IMAGES,
+              src_area=crop_src_area(c, s, r, synth.SRC_W, synth.SRC_H).mean(),
+              host=dict(center=c, scale=s, rot=r, joints=js, vis=vis, images=imgs))
+    w, h = cfg.heatmap_size
+    C = cfg.channels
+    out = torch.empty((B, C, h, w), dtype=torch.float32, device=dev)
+    fl = torch.empty_like(out)
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    xs = torch.arange(w, device=dev).view(1, 1, 1, w)
+    ys = torch.arange(h, device=dev).view(1, 1, h, 1)
+    trip = cfg.target_type == "offset"
+    for lo in range(0, B, 1024):
+        m = min(1024, B - lo)
+        mux = torch.rand((m, K, 1, 1), device=dev, generator=g) * (w + 3) - 2
+        muy = torch.rand((m, K, 1, 1), device=dev, generator=g) * (h + 3) - 2
+        amp = torch.rand((m, K, 1, 1), device=dev, generator=g) * 0.8 + 0.2
+        d2 = (xs - mux) ** 2 + (ys - muy) ** 2
+        if trip:
+            keep = (d2 / cfg.kpd ** 2) <= 1
+            clean = torch.stack([amp * torch.exp(-d2 / 8.0),
+                                 torch.where(keep, (mux - xs) / cfg.kpd, torch.zeros_like(d2)),
+                                 torch.where(keep, (muy - ys) / cfg.kpd, torch.zeros_like(d2))], 2)
+            clean = clean.reshape(m, C, h, w)
+            nscale = torch.tensor([0.02, 0.05, 0.05], device=dev).repeat(K).view(1, C, 1, 1)
+        else:
+            clean = amp * torch.exp(-d2 / (2.0 * float(cfg.sigma) ** 2))
+            nscale = 0.02
+        mul = 255.0 if cfg.pre_div else 1.0
+        out[lo:lo + m] = (clean + (torch.rand(clean.shape, device=dev, generator=g) * 2 - 1) * nscale) * mul
+        cf = D.flip_back(clean.float().contiguous(), cfg.flip_pairs, trip)  # what the mirrored input yields
+        fl[lo:lo + m] = (cf + (torch.rand(clean.shape, device=dev, generator=g) * 2 - 1) * nscale) * mul
+    wl["out"], wl["flipped"] = out, fl
+    return wl
+
+
+# ----------------------------------------------------------------------------------------
+# CPU baseline: the numpy/cv2 port of the reference path on the host cores
+# ----------------------------------------------------------------------------------------
+def _cpu_worker(task):
+    """One worker = one core: the reference's per-person path on `n` persons (seeded)."""
+    cfg_id, seed, n = task
+    os.environ["OMP_NUM_THREADS"] = "1"
+    import cv2
+    cv2.setNumThreads(1)
+    from oracle import np_port as P
+    from udp_pose_b200 import synth
+    from udp_pose_b200.configs import CONFIGS
+    cfg = CONFIGS[cfg_id]
+    rng = np.random.default_rng(seed)
+    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+    c, s, r = synth.boxes(cfg, n, rng, rotate=True)
+    imgs = synth.source_images(2, rng)
+    K = cfg.num_joints
+    js = np.zeros((n, K, 3))
+    js[..., 0] = c[:, None, 0] + rng.uniform(-0.6, 0.6, (n, K)) * s[:, None, 0] * 200.0
+    js[..., 1] = c[:, None, 1] + rng.uniform(-0.6, 0.6, (n, K)) * s[:, None, 1] * 200.0
+    vis = np.ones((n, K, 3))
+    out, fl = synth.heatmaps(cfg, n, rng)
+    trip = cfg.target_type == "offset"
+    t0 = time.perf_counter()
+    for i in range(n):  # encode: one person per __getitem__ call
+        P.crop_person(imgs[i % 2], float(r[i]), c[i], s[i], W, H)
+        j = js[i].copy()
+        j[:, 0:2] = P.map_joints(j[:, 0:2], float(r[i]), c[i], s[i], W, H)
+        if cfg.target_type == "gaussian":
+            P.target_gaussian(j, vis[i], W, H, w, h, cfg.sigma)
+        elif trip:
+            P.target_offset(j, vis[i], W, H, w, h, cfg.kpd)
+        else:
+            P.labels_rsn(j, vis[i, :, 0], W, H, w, h)
+    bs = 32  # decode: per validation batch, as validate() does
+    with np.errstate(all="ignore"):
+        for lo in range(0, n, bs):
+            avg = P.unflip_average(out[lo:lo + bs], fl[lo:lo + bs], cfg.flip_pairs, trip)
+            P.final_preds(avg, c[lo:lo + bs], s[lo:lo + bs], "offset" if trip else "gaussian",
+                          cfg.kpd, cfg.post_process, cfg.pre_div)
+    return n, time.perf_counter() - t0
+
+
+def cpu_baseline(cfg_id, seconds, per_worker=None):
+    """persons/s of the CPU port on all host cores (one single-threaded process per core)."""
+    import multiprocessing as mp
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(cores) as pool:
+        if per_worker is None:
+            n0, t = pool.apply(_cpu_worker, ((cfg_id, 1, 8),))  # calibrate on one core
+            per_worker = max(8, min(512, int(seconds * 0.6 * n0 / t)))
+        t0 = time.perf_counter()
+        res = pool.map(_cpu_worker, [(cfg_id, 100 + i, per_worker) for i in range(cores)])
+        wall = time.perf_counter() - t0
+    n = sum(a for a, _ in res)
+    core_rate = float(np.mean([a / b for a, b in res]))
+    busy = max(b for _, b in res)  # slowest worker's timed region (input generation excluded)
+    return {"value": n / busy, "unit": UNIT, "cores": cores, "kind": "port",
+            "per_core": core_rate, "per_worker": per_worker,
+            "sample": "%d persons (%d per core x %d single-threaded processes) of the same cfg-%d "
+                      "encode+decode pass with oracle/np_port.py (numpy+cv2 restatement of the "
+                      "reference, checked against its golden vectors); value = persons / slowest worker's "
+                      "timed region (%.1f s); wall %.1f s incl. input generation"
+                      % (n, per_worker, cores, cfg_id, busy, wall)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (numpy/cv2 port; the Python tree itself cannot
+    travel to the GPU box) on all host cores.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from udp_pose_b200.configs import CONFIGS
+    cfg = CONFIGS[args.config]
+    steps = max(1, min(args.steps, 3))
+    vals = []
+    per = None
+    for i in range(min(args.warmup, 1) + steps):
+        r = cpu_baseline(args.config, args.cpu_seconds, per)
+        per = r["per_worker"]
+        if i >= min(args.warmup, 1):
+            vals.append(r)
+    v = float(np.mean([x["value"] for x in vals]))
+    n_step = per * vals[0]["cores"]
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * n_step / v,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64/u8",
+            "data": "synthetic",
+            "config": {"workload": cfg.name + " encode(crop+target)+decode(flip+vote)", "cfg": args.config,
+                       "persons_per_step": n_step, "note": "CPU arm does not scale with --gpus"},
+            "cpu_baseline": dict(vals[-1], value=v),
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------
+STAGES = ["warp_matrices", "crop", "rotate_points", "encode", "decode"]
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from udp_pose_b200 import _lib, device_api as D
+    from udp_pose_b200.configs import CONFIGS
+    from udp_pose_b200.pipeline import HostBatch, HostPipeline
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.load()
+    cfg = CONFIGS[args.config]
+    B, K = args.batch, cfg.num_joints
+    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+
+    wl = make_device_workload(cfg, B, rank, torch, D)
+    src = D.SourceImages(wl["images"], wl["image_index"])
+    crop = torch.empty((B, H, W, 3), dtype=torch.uint8, device="cuda")
+    tshape = (B, 5, K, h, w) if cfg.target_type == "rsn" else (B, cfg.channels, h, w)
+    target = torch.empty(tshape, dtype=torch.float32, device="cuda")
+    gathered = torch.empty((world * B, K, 3), dtype=torch.float32, device="cuda") if world > 1 else None
+    j3 = wl["joints"].clone()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 2)]
+          for _ in range(args.steps)]
+
+    def step(e=None):
+        if e: e[0].record()
+        M = D.warp_matrices(wl["center"], wl["scale"], wl["rot"], cfg.image_size)
+        if e: e[1].record()
+        D.crop_batch(src, M, cfg.image_size, out=crop)
+        if e: e[2].record()
+        D.rotate_points_batch(wl["joints"], wl["rot"], wl["center"], wl["scale"], cfg.image_size, out=j3)
+        if e: e[3].record()
+        D.encode_batch(cfg, j3, wl["vis"], out=target)
+        if e: e[4].record()
+        r = D.decode_batch(cfg, wl["out"], wl["flipped"], wl["center"], wl["scale"], want_packed=True)
+        if e: e[5].record()
+        if world > 1:  # the one collective of the path: gather the keypoints
+            dist.all_gather_into_tensor(gathered, r["packed"])
+        if e: e[6].record()
+        return r
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    barrier()
+    t0 = time.time()
+    for i in range(args.steps):
+        step(ev[i])
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    step_ms = sum(e[0].elapsed_time(e[-1]) for e in ev)  # device time of the K steps, this rank
+    # device time from the first event of step 0 to the last event of the last step
+    total_ms = ev[0][0].elapsed_time(ev[-1][-1])
+    stage_ms = {nm: sum(e[i].elapsed_time(e[i + 1]) for e in ev) / args.steps for i, nm in enumerate(STAGES)}
+    stage_ms["gather"] = sum(e[5].elapsed_time(e[6]) for e in ev) / args.steps
+    tt = torch.tensor([total_ms, step_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    total_ms = float(tt[0])
+
+    # ---- end to end through host buffers (pinned), H2D and D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        del target, crop
+        torch.cuda.empty_cache()
+        nb = args.e2e_batch
+        hb = HostBatch(cfg, nb, N_IMAGES)
+        hs = wl["host"]
+        hb.images.copy_(torch.from_numpy(hs["images"]))
+        hb.image_index[:] = np.arange(nb) % N_IMAGES
+        for dst, key in ((hb.center, "center"), (hb.scale, "scale"), (hb.rot, "rot"),
+                         (hb.joints, "joints"), (hb.joints_vis, "vis")):
+            dst.copy_(torch.from_numpy(hs[key][:nb]))
+        hb.out.copy_(wl["out"][:nb])
+        hb.out_flipped.copy_(wl["flipped"][:nb])
+        pipe = HostPipeline(cfg, args.e2e_chunk, N_IMAGES)
+        for _ in range(3):
+            pipe.run(hb)
+        barrier()
+        e_steps = max(3, min(args.steps, 10))
+        pipe.launches = 0
+        ts = time.perf_counter()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(e_steps):
+            pipe.run(hb)
+        b.record()
+        barrier()
+        wall = time.perf_counter() - ts
+        ems = max(a.elapsed_time(b), wall * 1e3)
+        te = torch.tensor([ems], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * nb * e_steps / (float(te[0]) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": hb.h2d_bytes(), "d2h_bytes_per_step": hb.d2h_bytes(),
+               "persons_per_step_per_gpu": nb, "steps": e_steps, "chunk": args.e2e_chunk,
+               "api": "udp_pose_b200.pipeline.HostPipeline.run (pinned host in -> H2D -> 5 kernels via the C ABI -> D2H: crop, target, target_weight, keypoints)",
+               "launches": pipe.launches}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    ab = algorithmic_bytes(cfg, wl["src_area"])
+    kern = {}
+    for nm in STAGES:
+        gbs = ab[nm] * B / (stage_ms[nm] * 1e-3) / 1e9
+        kern[nm] = {"ms": round(stage_ms[nm], 4), "bytes_per_person": round(ab[nm], 1),
+                    "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
+    kern["decode"]["survey_bytes_per_person"] = ab["decode_survey"]
+    kern["decode"]["frac_on_survey_bytes"] = round(ab["decode_survey"] * B / (stage_ms["decode"] * 1e-3) / 1e9 / peak, 4)
+    dom = max(STAGES, key=lambda n: stage_ms[n])
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": peak,
+                "unit": "GB/s", "frac": kern[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": ab[dom] * B}
+    value = world * B * args.steps / (total_ms * 1e-3)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 maps / f64 joint prologue / u8 crop", "data": "synthetic",
+            "config": {"workload": cfg.name + ": crop 256x192 + UDPv1 offset target (KPD 3.5) + flip-test offset-vote decode, 51x64x48 maps",
+                       "cfg": args.config, "persons_per_gpu_per_step": B, "sharding": "contiguous persons per rank, one all_gather of [B,K,3] keypoints per step",
+                       "l2": "inputs larger than L2 (%.1f GB of network outputs per step per GPU)" % (2 * cfg.channels * h * w * 4 * B / 1e9)},
+            "roofline": roofline, "kernels": kern,
+            "gather_ms": round(stage_ms["gather"], 4),
+            "gpu_launches": len(STAGES) * args.steps,
+            "clocks": clocks}
+    if e2e:
+        line["e2e"] = e2e
+    if not args.no_cpu and world == 1:
+        line["cpu_baseline"] = cpu_baseline(args.config, args.cpu_seconds)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

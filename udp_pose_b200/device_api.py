@@ -110,15 +110,19 @@ def crop_batch(src, M, image_size, out=None):
     return out
 
 
-def rotate_points_batch(joints, rot_deg, center, scale, image_size, do_clip=False):
-    """a3 rotate_points on joints [N,K,>=2] float64 -> float64 [N,K,2]."""
+def rotate_points_batch(joints, rot_deg, center, scale, image_size, do_clip=False, out=None):
+    """a3 rotate_points on joints [N,K,>=2] float64 -> float64 [N,K,2] (or into `out`
+    [N,K,>=2], whose columns 0,1 are written)."""
     joints = _dev(joints, _F64)
     center, scale, f64 = _cs(center, scale)
     N, K, js = joints.shape
     rot = _dev(rot_deg, _F64) if rot_deg is not None else None
-    out = torch.empty((N, K, 2), dtype=_F64, device=joints.device)
+    if out is None:
+        out = torch.empty((N, K, 2), dtype=_F64, device=joints.device)
+    assert out.dtype == _F64 and out.is_contiguous() and out.shape[:2] == (N, K)
     _lib.call("udp_rotate_points", _ptr(joints), js, _ptr(rot), _ptr(center), _ptr(scale), f64,
-              int(image_size[0]), int(image_size[1]), int(do_clip), _ptr(out), 2, K, N, _stream())
+              int(image_size[0]), int(image_size[1]), int(do_clip), _ptr(out), out.shape[2], K, N,
+              _stream())
     return out
 
 

@@ -1,0 +1,135 @@
+"""Host-buffer entry point: the whole codec pass (crop -> target encode -> flip-fused decode)
+for a batch of persons whose inputs and outputs live in HOST memory.
+
+This is the call a user of the reference makes when the surrounding program still keeps its
+data in numpy (the reference's own calling convention): inputs are copied
+host->device, the kernels run through the C ABI, results are copied device->host.  The batch
+is cut into chunks that flow through three CUDA streams (upload / compute / download) with
+double-buffered device staging, so PCIe transfers in both directions overlap the kernels.
+
+bench.py times this as `e2e`.  Nothing here falls back to the CPU.
+"""
+import numpy as np
+import torch
+
+from . import device_api as D
+
+
+def pinned(shape, dtype):
+    return torch.empty(shape, dtype=dtype, pin_memory=True)
+
+
+class HostBatch:
+    """Pinned host buffers for one batch of `n` persons of a CodecConfig (inputs + outputs)."""
+
+    def __init__(self, cfg, n, n_images, src_hw=(480, 640)):
+        K, C = cfg.num_joints, cfg.channels
+        (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+        cs = torch.float64 if cfg.cs_dtype == "float64" else torch.float32
+        self.cfg, self.n = cfg, n
+        # inputs
+        self.images = pinned((n_images, src_hw[0], src_hw[1], 3), torch.uint8)
+        self.image_index = np.zeros(n, np.int64)
+        self.center = pinned((n, 2), cs)
+        self.scale = pinned((n, 2), cs)
+        self.rot = pinned((n,), torch.float64)
+        self.joints = pinned((n, K, 3), torch.float64)      # source-image coordinates
+        self.joints_vis = pinned((n, K, 3), torch.float64)
+        self.out = pinned((n, C, h, w), torch.float32)      # network output
+        self.out_flipped = pinned((n, C, h, w), torch.float32)
+        # outputs
+        self.crop = pinned((n, H, W, 3), torch.uint8)
+        tc = (len(D_RSN) * K) if cfg.target_type == "rsn" else C
+        self.target = pinned((n, tc, h, w), torch.float32)
+        self.target_weight = pinned((n, K, 1), torch.float32)
+        self.keypoints = pinned((n, K, 3), torch.float32)   # x, y, maxval (function.py:208-209)
+
+    def h2d_bytes(self):
+        t = [self.images, self.center, self.scale, self.rot, self.joints, self.joints_vis, self.out,
+             self.out_flipped]
+        return int(sum(x.numel() * x.element_size() for x in t))
+
+    def d2h_bytes(self):
+        t = [self.crop, self.target, self.target_weight, self.keypoints]
+        return int(sum(x.numel() * x.element_size() for x in t))
+
+
+from .configs import RSN_SIGMAS as D_RSN  # noqa: E402
+
+
+class HostPipeline:
+    """Chunked, stream-overlapped codec pass over a HostBatch."""
+
+    def __init__(self, cfg, chunk, n_images, src_hw=(480, 640), device="cuda"):
+        self.cfg, self.chunk, self.dev = cfg, chunk, torch.device(device)
+        K, C = cfg.num_joints, cfg.channels
+        (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+        cs = torch.float64 if cfg.cs_dtype == "float64" else torch.float32
+        dev = self.dev
+        self.s_up, self.s_run, self.s_down = (torch.cuda.Stream(dev) for _ in range(3))
+        self.images = torch.empty((n_images, src_hw[0], src_hw[1], 3), dtype=torch.uint8, device=dev)
+        tc = (len(D_RSN) * K) if cfg.target_type == "rsn" else C
+
+        def slot():
+            return dict(
+                center=torch.empty((chunk, 2), dtype=cs, device=dev),
+                scale=torch.empty((chunk, 2), dtype=cs, device=dev),
+                rot=torch.empty((chunk,), dtype=torch.float64, device=dev),
+                joints=torch.empty((chunk, K, 3), dtype=torch.float64, device=dev),
+                vis=torch.empty((chunk, K, 3), dtype=torch.float64, device=dev),
+                jcrop=torch.zeros((chunk, K, 3), dtype=torch.float64, device=dev),
+                out=torch.empty((chunk, C, h, w), dtype=torch.float32, device=dev),
+                fl=torch.empty((chunk, C, h, w), dtype=torch.float32, device=dev),
+                crop=torch.empty((chunk, H, W, 3), dtype=torch.uint8, device=dev),
+                target=torch.empty((chunk, tc, h, w), dtype=torch.float32, device=dev),
+                up=torch.cuda.Event(), ran=torch.cuda.Event(), down=torch.cuda.Event(),
+            )
+        self.slots = [slot(), slot()]
+        self.launches = 0
+
+    def run(self, hb):
+        """One pass over the HostBatch `hb`; results land in hb.crop/target/target_weight/keypoints.
+        Returns after everything is back on the host."""
+        cfg, n, chunk = self.cfg, hb.n, self.chunk
+        with torch.cuda.stream(self.s_up):
+            self.images.copy_(hb.images, non_blocking=True)
+        for ci, lo in enumerate(range(0, n, chunk)):
+            m = min(chunk, n - lo)
+            sl = self.slots[ci & 1]
+            sel = slice(lo, lo + m)
+            with torch.cuda.stream(self.s_up):
+                self.s_up.wait_event(sl["down"])  # slot free again (previous download finished)
+                for key, src in (("center", hb.center), ("scale", hb.scale), ("rot", hb.rot),
+                                 ("joints", hb.joints), ("vis", hb.joints_vis), ("out", hb.out),
+                                 ("fl", hb.out_flipped)):
+                    sl[key][:m].copy_(src[sel], non_blocking=True)
+                sl["up"].record()
+            with torch.cuda.stream(self.s_run):
+                self.s_run.wait_event(sl["up"])
+                src = D.SourceImages(self.images, hb.image_index[sel])
+                M = D.warp_matrices(sl["center"][:m], sl["scale"][:m], sl["rot"][:m], cfg.image_size)
+                D.crop_batch(src, M, cfg.image_size, out=sl["crop"][:m])
+                j3 = D.rotate_points_batch(sl["joints"][:m], sl["rot"][:m], sl["center"][:m],
+                                           sl["scale"][:m], cfg.image_size, out=sl["jcrop"][:m])
+                if cfg.target_type == "rsn":
+                    D.encode_batch(cfg, j3, sl["vis"][:m], out=sl["target"][:m].view(
+                        m, len(D_RSN), cfg.num_joints, *sl["target"].shape[2:]))
+                    tw = sl["vis"][:m, :, 0:1].float()
+                else:
+                    _, tw = D.encode_batch(cfg, j3, sl["vis"][:m], out=sl["target"][:m])
+                r = D.decode_batch(cfg, sl["out"][:m], sl["fl"][:m], sl["center"][:m], sl["scale"][:m],
+                                   want_packed=True)
+                self.launches += 5
+                sl["ran"].record()
+            with torch.cuda.stream(self.s_down):
+                self.s_down.wait_event(sl["ran"])
+                hb.crop[sel].copy_(sl["crop"][:m], non_blocking=True)
+                hb.target[sel].copy_(sl["target"][:m], non_blocking=True)
+                hb.target_weight[sel].copy_(tw, non_blocking=True)
+                hb.keypoints[sel].copy_(r["packed"], non_blocking=True)
+                sl["down"].record()
+                # keep the temporaries alive until the download stream is done with them
+                tw.record_stream(self.s_down)
+                r["packed"].record_stream(self.s_down)
+        self.s_down.synchronize()
+        self.s_run.synchronize()
