@@ -8,6 +8,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/udp_codec.h"
 
@@ -16,6 +17,14 @@
         cudaError_t e__ = cudaGetLastError();  \
         if (e__ != cudaSuccess) return (int)e__; \
     } while (0)
+
+// UDP_FORCE_GENERIC=1 in the environment routes the decoders through the shape-generic kernels
+// (used by the tests to cover both paths).
+inline bool udp_force_generic()
+{
+    const char *e = getenv("UDP_FORCE_GENERIC");
+    return e && e[0] == '1';
+}
 
 namespace udp {
 

@@ -15,7 +15,7 @@
 // the two windows (and their flipped counterparts) straight from global memory after the
 // argmax is known, and runs the same row-then-column FMA order on them: identical bits,
 // two thirds of the input tensor never leave HBM.
-#include "blur.cuh"
+#include "blur_fast.cuh"
 
 namespace udp {
 
@@ -31,45 +31,14 @@ struct DecodeOffsetArgs {
     float *packed;
 };
 
-__global__ void decode_offset_kernel(DecodeOffsetArgs p)
+// Everything after the blurred argmax: gather the two 7x7 offset windows, blur them at the
+// argmax, vote, inverse affine, store.  Called by all threads of the CTA.
+__device__ __forceinline__ void offset_finish(const DecodeOffsetArgs &p, long long map, int n,
+                                              const float *src, const float *fl, float bv, int bi)
 {
-    constexpr int R = 7, L = 8;
-    extern __shared__ __align__(16) float smem[];
-    __shared__ float red_v[32];
-    __shared__ int red_i[32];
     __shared__ float rowres[2][7];
     __shared__ float offs[2];
-
     const int w = p.w, h = p.h, hw = h * w;
-    const long long map = blockIdx.x;  // n*K + k
-    const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
-    float *A = smem;
-    float *T = A + (size_t)h * BlurGeom<R>::stride_a(w);
-
-    const float *src = p.out + (map * 3) * (long long)hw;  // channel (k, cls)
-    const int kp = p.out_flipped ? p.flip_perm[k] : k;
-    const float *fl = p.out_flipped ? p.out_flipped + (((long long)n * p.K + kp) * 3) * (long long)hw : nullptr;
-
-    float rv;
-    int ri;
-    load_tile<R>(src, fl, 1.0f, 0.0f, w, h, A, rv, ri);  // raw argmax unused in this mode
-    __syncthreads();
-    fill_pads<R>(A, w, h);
-    __syncthreads();
-    row_pass<R>(A, T, w, h);
-    __syncthreads();
-
-    float bv = -INFINITY;
-    int bi = 0x7fffffff;
-    col_pass<R, L>(T, w, h, [&](int y, int x, float4 s) {
-        const int base = y * w + x;
-        if (arg_better(s.x, base, bv, bi)) { bv = s.x; bi = base; }
-        if (arg_better(s.y, base + 1, bv, bi)) { bv = s.y; bi = base + 1; }
-        if (arg_better(s.z, base + 2, bv, bi)) { bv = s.z; bi = base + 2; }
-        if (arg_better(s.w, base + 3, bv, bi)) { bv = s.w; bi = base + 3; }
-    });
-    block_argmax(bv, bi, red_v, red_i);
-
     const bool mask = bv > 0.0f;
     const int ix = mask ? bi % w : 0, iy = mask ? bi / w : 0;
 
@@ -80,15 +49,17 @@ __global__ void decode_offset_kernel(DecodeOffsetArgs p)
         const float *a = src + (size_t)(1 + ch) * hw + (size_t)yy * w;
         const float *f = fl ? fl + (size_t)(1 + ch) * hw + (size_t)yy * w : nullptr;
         const float fs = ch == 0 ? -1.0f : 1.0f;  // x offsets change sign under the mirror (:40)
-        float s = 0.f;
+        float v[7];
 #pragma unroll
         for (int t = 0; t < 7; ++t) {
             const int xx = reflect101(ix - 3 + t, w);
-            float v = __ldg(a + xx);
-            if (f) v = __fmul_rn(__fadd_rn(v, fs * __ldg(f + (w - 1 - xx))), 0.5f);
-            v = __fmul_rn(v, p.kpd);  // :161-162
-            s = t == 0 ? __fmul_rn(v, Taps<3>::k(0)) : fmaf(v, Taps<3>::k(t), s);
+            v[t] = __ldg(a + xx);
+            if (f) v[t] = __fmul_rn(__fadd_rn(v[t], fs * __ldg(f + (w - 1 - xx))), 0.5f);
+            v[t] = __fmul_rn(v[t], p.kpd);  // :161-162
         }
+        float s = __fmul_rn(v[0], Taps<3>::k(0));
+#pragma unroll
+        for (int t = 1; t < 7; ++t) s = fmaf(v[t], Taps<3>::k(t), s);
         rowres[ch][i] = s;
     }
     __syncthreads();
@@ -122,6 +93,95 @@ __global__ void decode_offset_kernel(DecodeOffsetArgs p)
     }
 }
 
+// Generic path: any (w, h) with w % 4 == 0, NaN-exact argmax.
+__device__ __forceinline__ void decode_offset_generic(const DecodeOffsetArgs &p, float *smem,
+                                                      long long map, int n, const float *src,
+                                                      const float *fl)
+{
+    constexpr int R = 7, L = 8;
+    __shared__ float red_v[32];
+    __shared__ int red_i[32];
+    const int w = p.w, h = p.h;
+    float *A = smem;
+    float *T = A + (size_t)h * BlurGeom<R>::stride_a(w);
+    float rv;
+    int ri;
+    load_tile<R>(src, fl, 1.0f, 0.0f, w, h, A, rv, ri);  // raw argmax unused in this mode
+    __syncthreads();
+    fill_pads<R>(A, w, h);
+    __syncthreads();
+    row_pass<R>(A, T, w, h);
+    __syncthreads();
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    col_pass<R, L>(T, w, h, [&](int y, int x, float4 s) {
+        const int base = y * w + x;
+        if (arg_better(s.x, base, bv, bi)) { bv = s.x; bi = base; }
+        if (arg_better(s.y, base + 1, bv, bi)) { bv = s.y; bi = base + 1; }
+        if (arg_better(s.z, base + 2, bv, bi)) { bv = s.z; bi = base + 2; }
+        if (arg_better(s.w, base + 3, bv, bi)) { bv = s.w; bi = base + 3; }
+    });
+    block_argmax(bv, bi, red_v, red_i);
+    offset_finish(p, map, n, src, fl, bv, bi);
+}
+
+__global__ void decode_offset_kernel(DecodeOffsetArgs p)
+{
+    extern __shared__ __align__(16) float smem[];
+    const int hw = p.h * p.w;
+    const long long map = blockIdx.x;  // n*K + k
+    const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
+    const float *src = p.out + (map * 3) * (long long)hw;  // channel (k, cls)
+    const int kp = p.out_flipped ? p.flip_perm[k] : k;
+    const float *fl = p.out_flipped ? p.out_flipped + (((long long)n * p.K + kp) * 3) * (long long)hw : nullptr;
+    decode_offset_generic(p, smem, map, n, src, fl);
+}
+
+// Fast path: compile-time map shape, packed-FP32 blur (blur_fast.cuh).  Maps holding a
+// non-finite value are re-done by the generic path above (np.argmax's NaN rule).
+template <int W, int H, int NT>
+__global__ void __launch_bounds__(NT) decode_offset_fast_kernel(DecodeOffsetArgs p)
+{
+    constexpr int R = 7;
+    using G = FastGeom<W, H, R, NT>;
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float red_v[32];
+    __shared__ int red_i[32];
+    constexpr int hw = H * W;
+    const long long map = blockIdx.x;
+    const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
+    const float *src = p.out + (map * 3) * (long long)hw;
+    const int kp = p.out_flipped ? p.flip_perm[k] : k;
+    const float *fl = p.out_flipped ? p.out_flipped + (((long long)n * p.K + kp) * 3) * (long long)hw : nullptr;
+
+    float2 *A2 = reinterpret_cast<float2 *>(smem);
+    float *T = smem + G::A2_BYTES / 4;
+    float rv, fsum;
+    int ri;
+    fast_load<W, H, R, NT>(src, fl, 0.0f, A2, rv, ri, fsum);
+    if (__syncthreads_or(!(fabsf(fsum) < INFINITY))) {  // NaN / inf somewhere in the map
+        decode_offset_generic(p, smem, map, n, src, fl);
+        return;
+    }
+    fast_pads<W, H, R, NT>(A2);
+    __syncthreads();
+    fast_row_pass<W, H, R, NT>(A2, T);
+    __syncthreads();
+    float v0 = -INFINITY, v1 = -INFINITY;
+    int y0 = 0, y1 = 0, xc = 0;
+    fast_col_pass<W, H, R, NT>(T, [&](int y, int x, float2 s) {
+        xc = x;
+        if (s.x > v0) { v0 = s.x; y0 = y; }
+        if (s.y > v1) { v1 = s.y; y1 = y; }
+    });
+    float bv = v0;
+    int bi = y0 * W + xc;
+    if (arg_better(v1, y1 * W + xc + 1, bv, bi)) { bv = v1; bi = y1 * W + xc + 1; }
+    if (threadIdx.x >= G::CP * G::YS) { bv = -INFINITY; bi = 0x7fffffff; }
+    block_argmax(bv, bi, red_v, red_i);
+    offset_finish(p, map, n, src, fl, bv, bi);
+}
+
 }  // namespace udp
 
 extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
@@ -136,15 +196,32 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
         return UDP_EINVAL;
     udp::DecodeOffsetArgs a{out, out_flipped, flip_perm, (float)kpd, center, scale, cs_f64, K, w, h,
                             preds, maxvals, preds_in, argmax_idx, packed};
-    size_t smem = udp::BlurGeom<7>::smem_floats(w, h) * sizeof(float);
-    if (smem > 200 * 1024) return UDP_EINVAL;
-    cudaError_t e = cudaFuncSetAttribute(udp::decode_offset_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    const int threads = (h * w <= 4096) ? 128 : 256;
     long long maps = (long long)N * K;
     if (maps > 0x7fffffffLL) return UDP_EINVAL;
-    udp::decode_offset_kernel<<<(unsigned)maps, threads, smem, (cudaStream_t)stream>>>(a);
+    size_t gsmem = udp::BlurGeom<7>::smem_floats(w, h) * sizeof(float);
+    if (gsmem > 200 * 1024) return UDP_EINVAL;
+    if (!udp_force_generic()) {
+#define UDP_OFF_FAST(WW, HH, NT)                                                                 \
+        if (w == WW && h == HH) {                                                                \
+            using G = udp::FastGeom<WW, HH, 7, NT>;                                                \
+            size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                                       \
+            auto kern = udp::decode_offset_fast_kernel<WW, HH, NT>;                                \
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            if (e != cudaSuccess) return (int)e;                                                   \
+            kern<<<(unsigned)maps, NT, smem, (cudaStream_t)stream>>>(a);                           \
+            UDP_LAUNCH_CHECK();                                                                    \
+            return 0;                                                                              \
+        }
+        UDP_OFF_FAST(48, 64, 64)
+        UDP_OFF_FAST(64, 64, 64)
+        UDP_OFF_FAST(72, 96, 128)
+#undef UDP_OFF_FAST
+    }
+    cudaError_t e = cudaFuncSetAttribute(udp::decode_offset_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);
+    if (e != cudaSuccess) return (int)e;
+    const int threads = (h * w <= 4096) ? 128 : 256;
+    udp::decode_offset_kernel<<<(unsigned)maps, threads, gsmem, (cudaStream_t)stream>>>(a);
     UDP_LAUNCH_CHECK();
     return 0;
 }
