@@ -55,46 +55,77 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
     const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
     const int row_bytes = W * 3;
 
-    for (int p = threadIdx.x; p < rows * W; p += CROP_THREADS) {
-        int r = p / W, x = p - r * W;
-        int X = (X0[r] + ad[x]) >> 5, Y = (Y0[r] + bd[x]) >> 5;
-        int sx = X >> 5, sy = Y >> 5;
-        uint32_t fx = X & 31, fy = Y & 31;
-        // dp4a weight vectors: row 0 taps in bytes 0,1 ; row 1 taps in bytes 2,3
-        uint32_t wx = (32u - fx) | (fx << 8);
-        uint32_t a0, a1, a2;  // [p00 p01 p10 p11] per channel
-        if (sx >= 0 && sy >= 0 && sx + 1 < sw && sy + 1 < sh) {
-            const uint8_t *q0 = src + (size_t)sy * ss + sx * 3;
-            const uint8_t *q1 = q0 + ss;
-            uint32_t r0 = ldg_u8(q0), g0 = ldg_u8(q0 + 1), b0 = ldg_u8(q0 + 2);
-            uint32_t r1 = ldg_u8(q0 + 3), g1 = ldg_u8(q0 + 4), b1 = ldg_u8(q0 + 5);
-            uint32_t r2 = ldg_u8(q1), g2 = ldg_u8(q1 + 1), b2 = ldg_u8(q1 + 2);
-            uint32_t r3 = ldg_u8(q1 + 3), g3 = ldg_u8(q1 + 4), b3 = ldg_u8(q1 + 5);
-            a0 = r0 | (r1 << 8) | (r2 << 16) | (r3 << 24);
-            a1 = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
-            a2 = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
-        } else {
-            bool x0 = sx >= 0 && sx < sw, x1 = sx + 1 >= 0 && sx + 1 < sw;
-            bool y0 = sy >= 0 && sy < sh, y1 = sy + 1 >= 0 && sy + 1 < sh;
-            a0 = a1 = a2 = 0;
-            if (y0 && x0) { const uint8_t *q = src + (size_t)sy * ss + sx * 3;
-                a0 |= ldg_u8(q); a1 |= ldg_u8(q + 1); a2 |= ldg_u8(q + 2); }
-            if (y0 && x1) { const uint8_t *q = src + (size_t)sy * ss + (sx + 1) * 3;
-                a0 |= ldg_u8(q) << 8; a1 |= ldg_u8(q + 1) << 8; a2 |= ldg_u8(q + 2) << 8; }
-            if (y1 && x0) { const uint8_t *q = src + (size_t)(sy + 1) * ss + sx * 3;
-                a0 |= ldg_u8(q) << 16; a1 |= ldg_u8(q + 1) << 16; a2 |= ldg_u8(q + 2) << 16; }
-            if (y1 && x1) { const uint8_t *q = src + (size_t)(sy + 1) * ss + (sx + 1) * 3;
-                a0 |= ldg_u8(q) << 24; a1 |= ldg_u8(q + 1) << 24; a2 |= ldg_u8(q + 2) << 24; }
+    // Work item = 4 adjacent output pixels of one row (12 output bytes = three 32-bit words).
+    const int W4 = W >> 2;
+    const bool w4ok = (W & 3) == 0;
+    const int items = w4ok ? rows * W4 : 0;
+    for (int it = threadIdx.x; it < items; it += CROP_THREADS) {
+        const int r = it / W4, xb = (it - r * W4) << 2;
+        const int Xr = X0[r], Yr = Y0[r];
+        uint32_t px[4];  // r | g<<8 | b<<16 per pixel
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int x = xb + j;
+            const int X = (Xr + ad[x]) >> 5, Y = (Yr + bd[x]) >> 5;
+            const int sx = X >> 5, sy = Y >> 5;
+            const uint32_t fx = X & 31, fy = Y & 31;
+            const uint32_t wx = (32u - fx) | (fx << 8), wxh = wx << 16;
+            uint32_t a0, g0, g1;  // a0 = [r00 r01 r10 r11]; g0/g1 = [g0 g1 b0 b1] of source row 0/1
+            bool fast = sx >= 1 && sy >= 0 && sx + 4 < sw && sy + 1 < sh;
+            if (fast) {
+                // 6 contiguous bytes per source row, fetched as three aligned words and realigned
+                const uint8_t *p0 = src + (size_t)sy * ss + sx * 3;
+                const uint8_t *p1 = p0 + ss;
+                const uint32_t s0 = ((uint32_t)(uintptr_t)p0 & 3u) * 8u, s1 = ((uint32_t)(uintptr_t)p1 & 3u) * 8u;
+                const uint32_t *q0 = reinterpret_cast<const uint32_t *>((uintptr_t)p0 & ~(uintptr_t)3);
+                const uint32_t *q1 = reinterpret_cast<const uint32_t *>((uintptr_t)p1 & ~(uintptr_t)3);
+                const uint32_t u0 = __ldg(q0), u1 = __ldg(q0 + 1), u2 = __ldg(q0 + 2);
+                const uint32_t v0 = __ldg(q1), v1 = __ldg(q1 + 1), v2 = __ldg(q1 + 2);
+                const uint32_t lo0 = __funnelshift_r(u0, u1, s0), hi0 = __funnelshift_r(u1, u2, s0);
+                const uint32_t lo1 = __funnelshift_r(v0, v1, s1), hi1 = __funnelshift_r(v1, v2, s1);
+                a0 = __byte_perm(lo0, lo1, 0x7430);
+                g0 = __byte_perm(lo0, hi0, 0x5241);
+                g1 = __byte_perm(lo1, hi1, 0x5241);
+            } else {
+                const bool x0 = sx >= 0 && sx < sw, x1 = sx + 1 >= 0 && sx + 1 < sw;
+                const bool y0 = sy >= 0 && sy < sh, y1 = sy + 1 >= 0 && sy + 1 < sh;
+                uint32_t c00 = 0, c01 = 0, c10 = 0, c11 = 0;  // r | g<<8 | b<<16 of the four taps
+                if (y0 && x0) { const uint8_t *q = src + (size_t)sy * ss + sx * 3; c00 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+                if (y0 && x1) { const uint8_t *q = src + (size_t)sy * ss + (sx + 1) * 3; c01 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+                if (y1 && x0) { const uint8_t *q = src + (size_t)(sy + 1) * ss + sx * 3; c10 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+                if (y1 && x1) { const uint8_t *q = src + (size_t)(sy + 1) * ss + (sx + 1) * 3; c11 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+                a0 = (c00 & 255u) | (c01 & 255u) << 8 | (c10 & 255u) << 16 | (c11 & 255u) << 24;
+                g0 = __byte_perm(c00, c01, 0x6251);
+                g1 = __byte_perm(c10, c11, 0x6251);
+            }
+            const uint32_t wy0 = 32u - fy;
+            const uint32_t Sr = wy0 * __dp4a(a0, wx, 0u) + (fy * __dp4a(a0, wxh, 0u) + 512u);
+            const uint32_t Sg = wy0 * __dp4a(g0, wx, 0u) + (fy * __dp4a(g1, wx, 0u) + 512u);
+            const uint32_t Sb = wy0 * __dp4a(g0, wxh, 0u) + (fy * __dp4a(g1, wxh, 0u) + 512u);
+            px[j] = (Sr >> 10) | (Sg >> 10) << 8 | (Sb >> 10) << 16;
         }
-        uint32_t wy0 = 32u - fy;
-        uint32_t h0, h1, S;
-        uint8_t *o = tile + r * row_bytes + x * 3;
-        h0 = __dp4a(a0, wx, 0u); h1 = __dp4a(a0, wx << 16, 0u);
-        S = wy0 * h0 + fy * h1; o[0] = (uint8_t)((S + 512u) >> 10);
-        h0 = __dp4a(a1, wx, 0u); h1 = __dp4a(a1, wx << 16, 0u);
-        S = wy0 * h0 + fy * h1; o[1] = (uint8_t)((S + 512u) >> 10);
-        h0 = __dp4a(a2, wx, 0u); h1 = __dp4a(a2, wx << 16, 0u);
-        S = wy0 * h0 + fy * h1; o[2] = (uint8_t)((S + 512u) >> 10);
+        uint32_t *o = reinterpret_cast<uint32_t *>(tile + r * row_bytes + xb * 3);
+        o[0] = px[0] | px[1] << 24;
+        o[1] = px[1] >> 8 | px[2] << 16;
+        o[2] = px[2] >> 16 | px[3] << 8;
+    }
+    if (!w4ok) {  // generic widths: one pixel per thread, byte taps
+        for (int p = threadIdx.x; p < rows * W; p += CROP_THREADS) {
+            const int r = p / W, x = p - r * W;
+            const int X = (X0[r] + ad[x]) >> 5, Y = (Y0[r] + bd[x]) >> 5;
+            const int sx = X >> 5, sy = Y >> 5;
+            const uint32_t fx = X & 31, fy = Y & 31, wy0 = 32u - fy;
+            uint8_t *o = tile + r * row_bytes + x * 3;
+            for (int c = 0; c < 3; ++c) {
+                uint32_t t[4];
+                for (int k = 0; k < 4; ++k) {
+                    const int yy = sy + (k >> 1), xx = sx + (k & 1);
+                    t[k] = (yy >= 0 && yy < sh && xx >= 0 && xx < sw) ? ldg_u8(src + (size_t)yy * ss + xx * 3 + c) : 0u;
+                }
+                const uint32_t S = wy0 * ((32u - fx) * t[0] + fx * t[1]) + fy * ((32u - fx) * t[2] + fx * t[3]);
+                o[c] = (uint8_t)((S + 512u) >> 10);
+            }
+        }
     }
     __syncthreads();
 
