@@ -23,6 +23,31 @@ constexpr int CROP_THREADS = 256;
 
 __device__ __forceinline__ uint32_t ldg_u8(const uint8_t *p) { return (uint32_t)__ldg(p); }
 
+// Border pixel (some of the 2x2 taps fall outside the image): per-tap bounds checks, byte loads.
+// Kept out of line so the interior path stays branch- and predicate-free.
+__device__ __noinline__ uint32_t crop_border_pixel(const uint8_t *src, int sh, int sw, int ss, int Xq10, int Yq10)
+{
+    const int X = Xq10 >> 5, Y = Yq10 >> 5;
+    const int sx = X >> 5, sy = Y >> 5;
+    if (sx < -1 || sx >= sw || sy < -1 || sy >= sh) return 0u;  // all four taps outside
+    const uint32_t fx = X & 31, fy = Y & 31, wy0 = 32u - fy;
+    const bool x0 = sx >= 0, x1 = sx + 1 < sw, y0 = sy >= 0, y1 = sy + 1 < sh;
+    uint32_t c[4] = {0u, 0u, 0u, 0u};  // r | g<<8 | b<<16 of the taps 00 01 10 11
+    if (y0 && x0) { const uint8_t *q = src + (size_t)sy * ss + sx * 3; c[0] = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+    if (y0 && x1) { const uint8_t *q = src + (size_t)sy * ss + (sx + 1) * 3; c[1] = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+    if (y1 && x0) { const uint8_t *q = src + (size_t)(sy + 1) * ss + sx * 3; c[2] = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+    if (y1 && x1) { const uint8_t *q = src + (size_t)(sy + 1) * ss + (sx + 1) * 3; c[3] = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
+    uint32_t o = 0;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        const uint32_t t0 = (c[0] >> (8 * ch)) & 255u, t1 = (c[1] >> (8 * ch)) & 255u;
+        const uint32_t t2 = (c[2] >> (8 * ch)) & 255u, t3 = (c[3] >> (8 * ch)) & 255u;
+        const uint32_t S = wy0 * ((32u - fx) * t0 + fx * t1) + fy * ((32u - fx) * t2 + fx * t3);
+        o |= ((S + 512u) >> 10) << (8 * ch);
+    }
+    return o;
+}
+
 __global__ void __launch_bounds__(CROP_THREADS)
 warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                       const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H)
@@ -56,58 +81,57 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
     const int row_bytes = W * 3;
 
     // Work item = 4 adjacent output pixels of one row (12 output bytes = three 32-bit words).
+    // All source addressing is 32-bit byte offsets from the 4-byte-aligned image base.
     const int W4 = W >> 2;
     const bool w4ok = (W & 3) == 0;
     const int items = w4ok ? rows * W4 : 0;
+    const uint8_t *src_al = reinterpret_cast<const uint8_t *>((uintptr_t)src & ~(uintptr_t)3);
+    const int mis = (int)((uintptr_t)src & 3);
+    const uint32_t sw5 = sw > 5 ? (uint32_t)(sw - 5) : 0u, sh1 = sh > 1 ? (uint32_t)(sh - 1) : 0u;
+    int r = threadIdx.x / W4, xq = threadIdx.x - r * W4;
+    const int dr = CROP_THREADS / W4, dq = CROP_THREADS - dr * W4;
     for (int it = threadIdx.x; it < items; it += CROP_THREADS) {
-        const int r = it / W4, xb = (it - r * W4) << 2;
+        const int xb = xq << 2;
         const int Xr = X0[r], Yr = Y0[r];
-        uint32_t px[4];  // r | g<<8 | b<<16 per pixel
+        const int4 a4 = *reinterpret_cast<const int4 *>(ad + xb), b4 = *reinterpret_cast<const int4 *>(bd + xb);
+        const int Xs[4] = {Xr + a4.x, Xr + a4.y, Xr + a4.z, Xr + a4.w};
+        const int Ys[4] = {Yr + b4.x, Yr + b4.y, Yr + b4.z, Yr + b4.w};
+        uint32_t px[4];  // byte 0,1,2 = r,g,b
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const int x = xb + j;
-            const int X = (Xr + ad[x]) >> 5, Y = (Yr + bd[x]) >> 5;
-            const int sx = X >> 5, sy = Y >> 5;
-            const uint32_t fx = X & 31, fy = Y & 31;
-            const uint32_t wx = (32u - fx) | (fx << 8), wxh = wx << 16;
-            uint32_t a0, g0, g1;  // a0 = [r00 r01 r10 r11]; g0/g1 = [g0 g1 b0 b1] of source row 0/1
-            bool fast = sx >= 1 && sy >= 0 && sx + 4 < sw && sy + 1 < sh;
-            if (fast) {
-                // 6 contiguous bytes per source row, fetched as three aligned words and realigned
-                const uint8_t *p0 = src + (size_t)sy * ss + sx * 3;
-                const uint8_t *p1 = p0 + ss;
-                const uint32_t s0 = ((uint32_t)(uintptr_t)p0 & 3u) * 8u, s1 = ((uint32_t)(uintptr_t)p1 & 3u) * 8u;
-                const uint32_t *q0 = reinterpret_cast<const uint32_t *>((uintptr_t)p0 & ~(uintptr_t)3);
-                const uint32_t *q1 = reinterpret_cast<const uint32_t *>((uintptr_t)p1 & ~(uintptr_t)3);
+            const int X = Xs[j], Y = Ys[j];
+            const int sx = X >> 10, sy = Y >> 10;
+            // interior: 1 <= sx, sx + 4 < sw, 0 <= sy, sy + 1 < sh (keeps the 12-byte reads inside the image)
+            if ((uint32_t)(sx - 1) < sw5 && (uint32_t)sy < sh1) {
+                const uint32_t fx = ((uint32_t)X >> 5) & 31u, fy6 = ((uint32_t)Y << 1) & 0x7c0u;  // fy * 64
+                const uint32_t wx = (32u - fx) | (fx << 8), wxh = wx << 16;
+                const int o0 = sy * ss + (sx * 3 + mis), o1 = o0 + ss;
+                const uint32_t *q0 = reinterpret_cast<const uint32_t *>(src_al + (o0 & ~3));
+                const uint32_t *q1 = reinterpret_cast<const uint32_t *>(src_al + (o1 & ~3));
                 const uint32_t u0 = __ldg(q0), u1 = __ldg(q0 + 1), u2 = __ldg(q0 + 2);
                 const uint32_t v0 = __ldg(q1), v1 = __ldg(q1 + 1), v2 = __ldg(q1 + 2);
+                const uint32_t s0 = (uint32_t)o0 << 3, s1 = (uint32_t)o1 << 3;  // funnel shift uses bits 0..4
                 const uint32_t lo0 = __funnelshift_r(u0, u1, s0), hi0 = __funnelshift_r(u1, u2, s0);
                 const uint32_t lo1 = __funnelshift_r(v0, v1, s1), hi1 = __funnelshift_r(v1, v2, s1);
-                a0 = __byte_perm(lo0, lo1, 0x7430);
-                g0 = __byte_perm(lo0, hi0, 0x5241);
-                g1 = __byte_perm(lo1, hi1, 0x5241);
+                const uint32_t a0 = __byte_perm(lo0, lo1, 0x7430);  // [r00 r01 r10 r11]
+                const uint32_t g0 = __byte_perm(lo0, hi0, 0x5241);  // [g00 g01 b00 b01]
+                const uint32_t g1 = __byte_perm(lo1, hi1, 0x5241);  // [g10 g11 b10 b11]
+                // (S + 512) >> 10 == byte 2 of (64*S + 32768): no shifts, PRMT picks the byte
+                const uint32_t wy6 = 2048u - fy6;
+                const uint32_t Sr = wy6 * __dp4a(a0, wx, 0u) + (fy6 * __dp4a(a0, wxh, 0u) + 32768u);
+                const uint32_t Sg = wy6 * __dp4a(g0, wx, 0u) + (fy6 * __dp4a(g1, wx, 0u) + 32768u);
+                const uint32_t Sb = wy6 * __dp4a(g0, wxh, 0u) + (fy6 * __dp4a(g1, wxh, 0u) + 32768u);
+                px[j] = __byte_perm(__byte_perm(Sr, Sg, 0x4462), Sb, 0x4610);
             } else {
-                const bool x0 = sx >= 0 && sx < sw, x1 = sx + 1 >= 0 && sx + 1 < sw;
-                const bool y0 = sy >= 0 && sy < sh, y1 = sy + 1 >= 0 && sy + 1 < sh;
-                uint32_t c00 = 0, c01 = 0, c10 = 0, c11 = 0;  // r | g<<8 | b<<16 of the four taps
-                if (y0 && x0) { const uint8_t *q = src + (size_t)sy * ss + sx * 3; c00 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
-                if (y0 && x1) { const uint8_t *q = src + (size_t)sy * ss + (sx + 1) * 3; c01 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
-                if (y1 && x0) { const uint8_t *q = src + (size_t)(sy + 1) * ss + sx * 3; c10 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
-                if (y1 && x1) { const uint8_t *q = src + (size_t)(sy + 1) * ss + (sx + 1) * 3; c11 = ldg_u8(q) | ldg_u8(q + 1) << 8 | ldg_u8(q + 2) << 16; }
-                a0 = (c00 & 255u) | (c01 & 255u) << 8 | (c10 & 255u) << 16 | (c11 & 255u) << 24;
-                g0 = __byte_perm(c00, c01, 0x6251);
-                g1 = __byte_perm(c10, c11, 0x6251);
+                px[j] = crop_border_pixel(src, sh, sw, ss, X, Y);
             }
-            const uint32_t wy0 = 32u - fy;
-            const uint32_t Sr = wy0 * __dp4a(a0, wx, 0u) + (fy * __dp4a(a0, wxh, 0u) + 512u);
-            const uint32_t Sg = wy0 * __dp4a(g0, wx, 0u) + (fy * __dp4a(g1, wx, 0u) + 512u);
-            const uint32_t Sb = wy0 * __dp4a(g0, wxh, 0u) + (fy * __dp4a(g1, wxh, 0u) + 512u);
-            px[j] = (Sr >> 10) | (Sg >> 10) << 8 | (Sb >> 10) << 16;
         }
         uint32_t *o = reinterpret_cast<uint32_t *>(tile + r * row_bytes + xb * 3);
-        o[0] = px[0] | px[1] << 24;
-        o[1] = px[1] >> 8 | px[2] << 16;
-        o[2] = px[2] >> 16 | px[3] << 8;
+        o[0] = __byte_perm(px[0], px[1], 0x4210);
+        o[1] = __byte_perm(px[1], px[2], 0x5421);
+        o[2] = __byte_perm(px[2], px[3], 0x6542);
+        r += dr; xq += dq;
+        if (xq >= W4) { xq -= W4; ++r; }
     }
     if (!w4ok) {  // generic widths: one pixel per thread, byte taps
         for (int p = threadIdx.x; p < rows * W; p += CROP_THREADS) {
