@@ -19,7 +19,6 @@
 namespace udp {
 
 constexpr int CROP_ROWS = 16;
-constexpr int CROP_THREADS = 256;
 
 __device__ __forceinline__ uint32_t ldg_u8(const uint8_t *p) { return (uint32_t)__ldg(p); }
 
@@ -48,7 +47,7 @@ __device__ __noinline__ uint32_t crop_border_pixel(const uint8_t *src, int sh, i
     return o;
 }
 
-__global__ void __launch_bounds__(CROP_THREADS)
+__global__ void __launch_bounds__(512)
 warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                       const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H)
 {
@@ -65,7 +64,7 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
     const float *m = M + 6 * (size_t)n;
     const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
 
-    for (int x = threadIdx.x; x < W; x += CROP_THREADS) {
+    for (int x = threadIdx.x; x < W; x += (int)blockDim.x) {
         ad[x] = __double2int_rn(__dmul_rn(__dmul_rn(m00, (double)x), 1024.0));
         bd[x] = __double2int_rn(__dmul_rn(__dmul_rn(m10, (double)x), 1024.0));
     }
@@ -80,27 +79,22 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
     const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
     const int row_bytes = W * 3;
 
-    // Work item = 4 adjacent output pixels of one row (12 output bytes = three 32-bit words).
-    // All source addressing is 32-bit byte offsets from the 4-byte-aligned image base.
-    const int W4 = W >> 2;
-    const bool w4ok = (W & 3) == 0;
-    const int items = w4ok ? rows * W4 : 0;
+    // Thread = output column x (consecutive lanes = consecutive x, so a warp's loads touch one
+    // or two 128-byte lines), looping over the CTA's rows with the column deltas in registers.
+    // ncu on the earlier 4-pixels-per-thread layout: LSU wavefronts at 75 % of peak with five
+    // wavefronts per request; on the 1-pixel-per-iteration layout ~98 instructions per pixel,
+    // half of them loop/index overhead -- hence this shape.
     const uint8_t *src_al = reinterpret_cast<const uint8_t *>((uintptr_t)src & ~(uintptr_t)3);
     const int mis = (int)((uintptr_t)src & 3);
     const uint32_t sw5 = sw > 5 ? (uint32_t)(sw - 5) : 0u, sh1 = sh > 1 ? (uint32_t)(sh - 1) : 0u;
-    int r = threadIdx.x / W4, xq = threadIdx.x - r * W4;
-    const int dr = CROP_THREADS / W4, dq = CROP_THREADS - dr * W4;
-    for (int it = threadIdx.x; it < items; it += CROP_THREADS) {
-        const int xb = xq << 2;
-        const int Xr = X0[r], Yr = Y0[r];
-        const int4 a4 = *reinterpret_cast<const int4 *>(ad + xb), b4 = *reinterpret_cast<const int4 *>(bd + xb);
-        const int Xs[4] = {Xr + a4.x, Xr + a4.y, Xr + a4.z, Xr + a4.w};
-        const int Ys[4] = {Yr + b4.x, Yr + b4.y, Yr + b4.z, Yr + b4.w};
-        uint32_t px[4];  // byte 0,1,2 = r,g,b
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int X = Xs[j], Y = Ys[j];
+    for (int x = threadIdx.x; x < W; x += (int)blockDim.x) {
+        const int adx = ad[x], bdx = bd[x];
+        uint8_t *o = tile + x * 3;
+#pragma unroll 4
+        for (int r = 0; r < rows; ++r, o += row_bytes) {
+            const int X = X0[r] + adx, Y = Y0[r] + bdx;  // Q10
             const int sx = X >> 10, sy = Y >> 10;
+            uint32_t px;  // byte 0,1,2 = r,g,b
             // interior: 1 <= sx, sx + 4 < sw, 0 <= sy, sy + 1 < sh (keeps the 12-byte reads inside the image)
             if ((uint32_t)(sx - 1) < sw5 && (uint32_t)sy < sh1) {
                 const uint32_t fx = ((uint32_t)X >> 5) & 31u, fy6 = ((uint32_t)Y << 1) & 0x7c0u;  // fy * 64
@@ -121,34 +115,11 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
                 const uint32_t Sr = wy6 * __dp4a(a0, wx, 0u) + (fy6 * __dp4a(a0, wxh, 0u) + 32768u);
                 const uint32_t Sg = wy6 * __dp4a(g0, wx, 0u) + (fy6 * __dp4a(g1, wx, 0u) + 32768u);
                 const uint32_t Sb = wy6 * __dp4a(g0, wxh, 0u) + (fy6 * __dp4a(g1, wxh, 0u) + 32768u);
-                px[j] = __byte_perm(__byte_perm(Sr, Sg, 0x4462), Sb, 0x4610);
+                px = __byte_perm(__byte_perm(Sr, Sg, 0x4462), Sb, 0x4610);
             } else {
-                px[j] = crop_border_pixel(src, sh, sw, ss, X, Y);
+                px = crop_border_pixel(src, sh, sw, ss, X, Y);
             }
-        }
-        uint32_t *o = reinterpret_cast<uint32_t *>(tile + r * row_bytes + xb * 3);
-        o[0] = __byte_perm(px[0], px[1], 0x4210);
-        o[1] = __byte_perm(px[1], px[2], 0x5421);
-        o[2] = __byte_perm(px[2], px[3], 0x6542);
-        r += dr; xq += dq;
-        if (xq >= W4) { xq -= W4; ++r; }
-    }
-    if (!w4ok) {  // generic widths: one pixel per thread, byte taps
-        for (int p = threadIdx.x; p < rows * W; p += CROP_THREADS) {
-            const int r = p / W, x = p - r * W;
-            const int X = (X0[r] + ad[x]) >> 5, Y = (Y0[r] + bd[x]) >> 5;
-            const int sx = X >> 5, sy = Y >> 5;
-            const uint32_t fx = X & 31, fy = Y & 31, wy0 = 32u - fy;
-            uint8_t *o = tile + r * row_bytes + x * 3;
-            for (int c = 0; c < 3; ++c) {
-                uint32_t t[4];
-                for (int k = 0; k < 4; ++k) {
-                    const int yy = sy + (k >> 1), xx = sx + (k & 1);
-                    t[k] = (yy >= 0 && yy < sh && xx >= 0 && xx < sw) ? ldg_u8(src + (size_t)yy * ss + xx * 3 + c) : 0u;
-                }
-                const uint32_t S = wy0 * ((32u - fx) * t[0] + fx * t[1]) + fy * ((32u - fx) * t[2] + fx * t[3]);
-                o[c] = (uint8_t)((S + 512u) >> 10);
-            }
+            o[0] = (uint8_t)px; o[1] = (uint8_t)(px >> 8); o[2] = (uint8_t)(px >> 16);
         }
     }
     __syncthreads();
@@ -159,9 +130,9 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
     if ((row_bytes & 15) == 0) {
         const int4 *t4 = reinterpret_cast<const int4 *>(tile);
         int4 *o4 = reinterpret_cast<int4 *>(out);
-        for (int i = threadIdx.x; i < total / 16; i += CROP_THREADS) __stcs(o4 + i, t4[i]);
+        for (int i = threadIdx.x; i < total / 16; i += (int)blockDim.x) __stcs(o4 + i, t4[i]);
     } else {
-        for (int i = threadIdx.x; i < total; i += CROP_THREADS) out[i] = tile[i];
+        for (int i = threadIdx.x; i < total; i += (int)blockDim.x) out[i] = tile[i];
     }
 }
 
@@ -181,10 +152,11 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
     }
+    const int threads = W <= 96 ? 96 : (W <= 512 ? ((W + 31) / 32) * 32 : 512);
     for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
         int nn = N - n0 < 65535 ? N - n0 : 65535;
         dim3 grid((H + udp::CROP_ROWS - 1) / udp::CROP_ROWS, nn);
-        udp::warp_affine_u8_kernel<<<grid, udp::CROP_THREADS, smem, (cudaStream_t)stream>>>(
+        udp::warp_affine_u8_kernel<<<grid, threads, smem, (cudaStream_t)stream>>>(
             src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
             dst + (size_t)n0 * H * W * 3, W, H);
         UDP_LAUNCH_CHECK();
