@@ -1,0 +1,394 @@
+"""The reference's own call surface for the codec path, served by the CUDA library.
+
+Every name below has the signature, argument meaning, return dtypes and error behaviour of
+the reference function it replaces; numpy arrays in, numpy arrays out.  Each
+call uploads its arguments, launches the kernels through the C ABI (udp_pose_b200.device_api
+-> libudp_codec.so) and downloads the result.  There is no CPU implementation behind these
+names: without a GPU or without the built library they raise (udp_pose_b200._lib.load).
+
+`install()` substitutes them into an imported deep_hrnet/lib tree (lib.core.inference,
+lib.utils.transforms, lib.dataset.JointsDataset); INTEGRATION.md shows the maintainer-side
+patch.  Differences from the reference that a caller can observe are listed in each
+docstring; the only deliberate ones are (1) inputs are never mutated except where the
+reference's callers rely on it (`post` still writes the blurred maps back), and (2)
+`get_final_preds` accepts CUDA tensors too and then skips the host round trip.
+
+For throughput use the batched device API directly: one launch per batch instead of one
+Python call per person (the reference's DataLoader-worker model).
+"""
+import copy
+import random
+
+import numpy as np
+import torch
+
+from . import device_api as D
+
+RSN_KERNEL_SIGMA = {15: 2.6, 11: 2.0, 9: 1.7, 7: 1.4105, 5: 1.1105}  # RSN/dataset/JointsDataset.py:19-25
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def _cs1(center, scale):
+    """One person's center/scale -> [1,2] arrays of one float dtype (float32 kept, else float64)."""
+    c, s = np.asarray(center), np.asarray(scale)
+    dt = np.float32 if (c.dtype == np.float32 and s.dtype == np.float32) else np.float64
+    return c.astype(dt).reshape(1, 2), s.astype(dt).reshape(1, 2)
+
+
+def _csN(center, scale):
+    c, s = np.asarray(center), np.asarray(scale)
+    dt = np.float32 if (c.dtype == np.float32 and s.dtype == np.float32) else np.float64
+    return np.ascontiguousarray(c, dt).reshape(-1, 2), np.ascontiguousarray(s, dt).reshape(-1, 2)
+
+
+# ------------------------------------------------------------------------------- crop side
+def get_warpmatrix(theta, size_input, size_dst, size_target):
+    """deep_hrnet/lib/dataset/JointsDataset.py:29-49.  theta degrees, size_input = 2*center,
+    size_dst = image_size - 1, size_target = scale (box/200).  -> float32 [2,3] (dst->src)."""
+    center = np.asarray(size_input) * 0.5  # exact inverse of the caller's c*2.0 (:226)
+    c, s = _cs1(center.astype(np.asarray(size_input).dtype, copy=False), size_target)
+    dst = np.asarray(size_dst, np.float64)
+    W, H = int(round(float(dst[0]) + 1.0)), int(round(float(dst[1]) + 1.0))
+    M = D.warp_matrices(c, s, np.array([float(theta)]), (W, H))
+    return _np(M)[0]
+
+
+def rotate_points(src_points, angle, c, dst_img_shape, size_target, do_clip=True):
+    """JointsDataset.py:51-73.  src_points [K,2] -> [K,2] of the same dtype."""
+    pts = np.asarray(src_points)
+    cc, ss = _cs1(c, size_target)
+    out = D.rotate_points_batch(np.ascontiguousarray(pts[None, :, :2], np.float64),
+                                np.array([float(angle)]), cc, ss,
+                                (int(dst_img_shape[0]), int(dst_img_shape[1])), do_clip=bool(do_clip))
+    return _np(out)[0].astype(pts.dtype, copy=False)
+
+
+def warp_affine(data_numpy, trans, dsize):
+    """cv2.warpAffine(data_numpy, trans, dsize, flags=WARP_INVERSE_MAP|INTER_LINEAR) for a
+    uint8 HWC3 image (call sites JointsDataset.py:227, RSN/dataset/JointsDataset.py:197)."""
+    img = np.asarray(data_numpy)
+    if img.dtype != np.uint8 or img.ndim != 3 or img.shape[2] != 3:
+        raise ValueError("warp_affine: expected a uint8 [H,W,3] image")
+    src = D.SourceImages([torch.from_numpy(np.ascontiguousarray(img))], [0])
+    M = np.ascontiguousarray(np.asarray(trans, np.float32).reshape(1, 2, 3))
+    return _np(D.crop_batch(src, M, (int(dsize[0]), int(dsize[1]))))[0]
+
+
+def fliplr_joints(joints, joints_vis, width, matched_parts):
+    """deep_hrnet/lib/utils/transforms.py:50-64 -> (joints*joints_vis, joints_vis).
+    The reference also flips its arguments in place; this does not."""
+    j, v = D.fliplr_joints_batch(np.asarray(joints, np.float64)[None], np.asarray(joints_vis, np.float64)[None],
+                                 int(width), matched_parts, mul_vis=True)
+    return _np(j)[0], _np(v)[0]
+
+
+def flip_joints(joints, joints_vis, width, pairs):
+    """RSN/lib/utils/transforms.py:70-79 (no visibility product)."""
+    j, v = D.fliplr_joints_batch(np.asarray(joints, np.float64)[None], np.asarray(joints_vis, np.float64)[None],
+                                 int(width), pairs, mul_vis=False)
+    return _np(j)[0], _np(v)[0]
+
+
+# ----------------------------------------------------------------------------- encode side
+def half_body_transform(ds, joints, joints_vis):
+    """JointsDataset.half_body_transform (:124-167): host-side box selection from the visible
+    upper- or lower-body joints; uses np.random exactly once, like the reference."""
+    vis = joints_vis[:, 0] > 0
+    upper = [joints[k] for k in range(ds.num_joints) if vis[k] and k in ds.upper_body_ids]
+    lower = [joints[k] for k in range(ds.num_joints) if vis[k] and k not in ds.upper_body_ids]
+    pick = upper if (np.random.randn() < 0.5 and len(upper) > 2) else (lower if len(lower) > 2 else upper)
+    if len(pick) < 2:
+        return None, None
+    pts = np.array(pick, dtype=np.float32)
+    center = pts.mean(axis=0)[:2]
+    lo, hi = np.amin(pts, axis=0), np.amax(pts, axis=0)
+    bw, bh = hi[0] - lo[0], hi[1] - lo[1]
+    if bw > ds.aspect_ratio * bh:
+        bh = bw * 1.0 / ds.aspect_ratio
+    elif bw < ds.aspect_ratio * bh:
+        bw = bh * ds.aspect_ratio
+    scale = np.array([bw * 1.0 / ds.pixel_std, bh * 1.0 / ds.pixel_std], dtype=np.float32) * 1.5
+    return center, scale
+
+
+class JointsDataset(torch.utils.data.Dataset):
+    """deep_hrnet/lib/dataset/JointsDataset.py:75-385 with the crop, the joint map and the
+    target generation on the GPU.  Constructor, attributes, `generate_target` and
+    `__getitem__` follow the reference; `get_batch` is the batched form (one launch per
+    stage for a whole list of records) that a B200 input pipeline should call instead."""
+
+    def __init__(self, cfg, root, image_set, is_train, transform=None):
+        self.num_joints = 0
+        self.pixel_std = 200
+        self.flip_pairs = []
+        self.parent_ids = []
+        self.is_train = is_train
+        self.root = root
+        self.image_set = image_set
+        self.output_path = getattr(cfg, "OUTPUT_DIR", "")
+        ds = cfg.DATASET
+        self.data_format = getattr(ds, "DATA_FORMAT", "jpg")
+        self.scale_factor = ds.SCALE_FACTOR
+        self.rotation_factor = ds.ROT_FACTOR
+        self.flip = ds.FLIP
+        self.num_joints_half_body = ds.NUM_JOINTS_HALF_BODY
+        self.prob_half_body = ds.PROB_HALF_BODY
+        self.color_rgb = ds.COLOR_RGB
+        if getattr(ds, "CUTOUT", None) or getattr(ds, "HIDE_AND_SEEK", None):
+            raise NotImplementedError("AID augmentations (Cutout / HideAndSeek) are outside the codec "
+                                      "path (SURVEY.md 8f rank 5); pass them as `transform`")
+        self.target_type = cfg.MODEL.TARGET_TYPE
+        self.image_size = np.array(cfg.MODEL.IMAGE_SIZE)
+        self.heatmap_size = np.array(cfg.MODEL.HEATMAP_SIZE)
+        self.sigma = cfg.MODEL.SIGMA
+        self.use_different_joints_weight = cfg.LOSS.USE_DIFFERENT_JOINTS_WEIGHT
+        self.joints_weight = 1
+        self.kpd = cfg.LOSS.KPD
+        self.transform = transform
+        self.db = []
+
+    def _get_db(self):
+        raise NotImplementedError
+
+    def evaluate(self, cfg, preds, output_dir, *args, **kwargs):
+        raise NotImplementedError
+
+    def __len__(self):
+        return len(self.db)
+
+    def half_body_transform(self, joints, joints_vis):
+        return half_body_transform(self, joints, joints_vis)
+
+    # -- a5 / a6 -----------------------------------------------------------------------
+    def generate_target_batch(self, joints, joints_vis):
+        """joints, joints_vis [N,K,3] -> CUDA tensors (target [N,C,h,w], target_weight [N,K,1])."""
+        assert self.target_type in ("gaussian", "offset"), "Only support gaussian map and offset now!"
+        jw = None
+        if self.use_different_joints_weight:
+            jw = np.ascontiguousarray(np.asarray(self.joints_weight, np.float32).reshape(-1))
+        img, hm = tuple(int(v) for v in self.image_size), tuple(int(v) for v in self.heatmap_size)
+        if self.target_type == "gaussian":
+            return D.encode_gaussian(joints, joints_vis, img, hm, float(self.sigma), jw)
+        return D.encode_offset(joints, joints_vis, img, hm, float(self.kpd), jw)
+
+    def generate_target(self, joints, joints_vis):
+        """JointsDataset.py:291-385 -> (target float32 [K or 3K,h,w], target_weight float32 [K,1])."""
+        t, tw = self.generate_target_batch(np.asarray(joints, np.float64)[None], np.asarray(joints_vis, np.float64)[None])
+        return _np(t)[0], _np(tw)[0]
+
+    # -- a8 ----------------------------------------------------------------------------
+    def _read(self, image_file):
+        import cv2
+        if self.data_format == "zip":
+            raise NotImplementedError("zip data format is outside the codec path")
+        img = cv2.imread(image_file, cv2.IMREAD_COLOR | cv2.IMREAD_IGNORE_ORIENTATION)
+        if img is None:
+            raise ValueError("Fail to read {}".format(image_file))
+        if self.color_rgb:
+            img = cv2.cvtColor(img, cv2.COLOR_BGR2RGB)
+        return img
+
+    def _augment(self, rec, img):
+        """The reference's random draws, in the reference's order (JointsDataset.py:206-224)."""
+        joints, joints_vis = rec["joints_3d"], rec["joints_3d_vis"]
+        c, s, r = rec["center"], rec["scale"], 0
+        if self.is_train:
+            if np.sum(joints_vis[:, 0]) > self.num_joints_half_body and np.random.rand() < self.prob_half_body:
+                ch, sh = self.half_body_transform(joints, joints_vis)
+                if ch is not None and sh is not None:
+                    c, s = ch, sh
+            sf, rf = self.scale_factor, self.rotation_factor
+            s = s * np.clip(np.random.randn() * sf + 1, 1 - sf, 1 + sf)
+            r = np.clip(np.random.randn() * rf, -rf * 2, rf * 2) if random.random() <= 0.6 else 0
+            if self.flip and random.random() <= 0.5:
+                img = img[:, ::-1, :]
+                joints, joints_vis = fliplr_joints(joints, joints_vis, img.shape[1], self.flip_pairs)
+                c = c.copy()
+                c[0] = img.shape[1] - c[0] - 1
+        return img, joints, joints_vis, c, s, r
+
+    def get_batch(self, indices, images=None):
+        """Batched __getitem__: returns (input uint8 CUDA [N,H,W,3], target CUDA, target_weight
+        CUDA, metas).  `images` (optional) supplies decoded uint8 arrays instead of files."""
+        W, H = int(self.image_size[0]), int(self.image_size[1])
+        recs, imgs, js, vs, cs, ss, rs = [], [], [], [], [], [], []
+        for n, idx in enumerate(indices):
+            rec = copy.deepcopy(self.db[idx])
+            img = images[n] if images is not None else self._read(rec["image"])
+            img, j, v, c, s, r = self._augment(rec, img)
+            recs.append(rec); imgs.append(torch.from_numpy(np.ascontiguousarray(img)))
+            js.append(j); vs.append(v); cs.append(c); ss.append(s); rs.append(float(r))
+        c, s = _csN(np.stack(cs), np.stack(ss))
+        rot = np.asarray(rs, np.float64)
+        M = D.warp_matrices(c, s, rot, (W, H))
+        inp = D.crop_batch(D.SourceImages(imgs, np.arange(len(imgs))), M, (W, H))
+        j = np.ascontiguousarray(np.stack(js), np.float64)
+        jd = torch.from_numpy(j).cuda()
+        D.rotate_points_batch(jd, rot, c, s, (W, H), do_clip=False, out=jd)
+        v = np.ascontiguousarray(np.stack(vs), np.float64)
+        target, tw = self.generate_target_batch(jd, v)
+        jh = _np(jd)
+        metas = []
+        for n, rec in enumerate(recs):
+            metas.append({"image": rec["image"], "filename": rec.get("filename", ""),
+                          "imgnum": rec.get("imgnum", ""), "joints": jh[n], "joints_vis": v[n],
+                          "center": cs[n], "scale": ss[n], "rotation": rs[n] if rs[n] else 0,
+                          "score": rec.get("score", 1)})
+        return inp, target, tw, metas
+
+    def __getitem__(self, idx, image=None):
+        inp, target, tw, metas = self.get_batch([idx], None if image is None else [image])
+        x = _np(inp)[0]
+        if self.transform:
+            x = self.transform(x)
+        return x, target[0].cpu(), tw[0].cpu(), metas[0]
+
+
+class RSNJointsEncoder:
+    """The codec half of RSN/dataset/JointsDataset.py (:193-220, :276-291): joint map with
+    visibility cull, then the five full-map 255*exp() labels."""
+
+    def __init__(self, keypoint_num, input_shape, output_shape, kernels=((15, 15), (11, 11), (9, 9), (7, 7), (5, 5))):
+        self.keypoint_num = keypoint_num
+        self.input_shape, self.output_shape = tuple(input_shape), tuple(output_shape)  # (H,W), (h,w)
+        self.gaussian_kernels = list(kernels)
+
+    def _sizes(self):
+        return (self.input_shape[1], self.input_shape[0]), (self.output_shape[1], self.output_shape[0])
+
+    def generate_heatmap(self, joints, valid, kernel=(7, 7)):
+        """-> float32 [K,h,w]; valid [K] or [K,1] (drawn iff >= 1)."""
+        img, hm = self._sizes()
+        v = np.asarray(valid, np.float32).reshape(1, -1)[:, :self.keypoint_num]
+        lab = D.encode_rsn(np.asarray(joints, np.float64)[None], v, img, hm, [RSN_KERNEL_SIGMA[kernel[0]]])
+        return _np(lab)[0, 0]
+
+    def labels(self, joints, valid):
+        """All label scales at once -> float32 [S,K,h,w] (the :214-220 loop)."""
+        img, hm = self._sizes()
+        v = np.asarray(valid, np.float32).reshape(1, -1)[:, :self.keypoint_num]
+        sig = [RSN_KERNEL_SIGMA[k[0]] for k in self.gaussian_kernels]
+        return _np(D.encode_rsn(np.asarray(joints, np.float64)[None], v, img, hm, sig))[0]
+
+    def transform_joints(self, joints, joints_vis, rotation, center, scale):
+        """get_warpmatrix_inverse + affine_transform + cull (:203-211) -> (joints, joints_vis, trans_inv)."""
+        img, _ = self._sizes()
+        j, v, Mi = D.rsn_transform_joints_batch(np.asarray(joints, np.float64)[None], np.asarray(joints_vis, np.float64)[None],
+                                                np.array([float(rotation)]), np.asarray(center, np.float32).reshape(1, 2),
+                                                np.asarray(scale, np.float32).reshape(1, 2), img)
+        return _np(j)[0], _np(v)[0], _np(Mi)[0]
+
+
+# ----------------------------------------------------------------------------- decode side
+def _check4(a, what):
+    assert isinstance(a, np.ndarray), "%s should be numpy.ndarray" % what
+    assert a.ndim == 4, "%s should be 4-ndim" % what
+
+
+def flip_back(output_flipped, matched_parts):
+    """deep_hrnet/lib/utils/transforms.py:15-29 (RSN/lib/utils/transforms.py:59-67).
+    Returns a new array; the reference returns a view of its (mutated) argument."""
+    assert output_flipped.ndim == 4, "output_flipped should be [batch_size, num_joints, height, width]"
+    return _np(D.flip_back(np.ascontiguousarray(output_flipped, np.float32), matched_parts, False))
+
+
+def flip_back_offset(output_flipped, matched_parts):
+    """transforms.py:31-47: mirror, negate the x-offset channels, swap joint triplets."""
+    assert output_flipped.ndim == 4, "output_flipped should be [batch_size, num_joints, height, width]"
+    return _np(D.flip_back(np.ascontiguousarray(output_flipped, np.float32), matched_parts, True))
+
+
+def get_max_preds(batch_heatmaps):
+    """deep_hrnet/lib/core/inference.py:30-58 -> (preds float32 [B,K,2], maxvals float32 [B,K,1])."""
+    _check4(batch_heatmaps, "batch_heatmaps")
+    r = D.decode_gaussian(np.ascontiguousarray(batch_heatmaps, np.float32), None, None, post_process=False)
+    return _np(r["preds"]), _np(r["maxvals"])
+
+
+def post(coords, batch_heatmaps):
+    """inference.py:60-145 -> float64 [B,K,2].  As in the reference the blurred, renormalised
+    maps are written back into `batch_heatmaps`.  `coords` must be get_max_preds(batch_heatmaps)[0]
+    -- the only way the reference calls it (:153-155); anything else raises ValueError."""
+    _check4(batch_heatmaps, "batch_heatmaps")
+    hm = np.ascontiguousarray(batch_heatmaps, np.float32)
+    with np.errstate(all="ignore"):
+        r = D.decode_gaussian(hm, None, None, post_process=True, want_idx=True, want_blurred=True)
+        idx = _np(r["idx"])
+        mv = _np(r["maxvals"])[..., 0]
+        w = hm.shape[3]
+        mine = np.stack([idx % w, idx // w], -1).astype(np.float32) * (mv > 0.0)[..., None]
+        if not np.array_equal(mine, np.asarray(coords, np.float32)):
+            raise ValueError("post(): coords is not get_max_preds(batch_heatmaps)[0]")
+    if batch_heatmaps.dtype == np.float32:
+        batch_heatmaps[...] = _np(r["blurred"])
+    return _np(r["preds"])
+
+
+def transform_preds(coords, center, scale, output_size):
+    """inference.py:20-27 (= utils/transforms.py:67-74) -> float64 [K,2]."""
+    co = np.asarray(coords)
+    if co.dtype not in (np.float32, np.float64):
+        co = co.astype(np.float64)
+    c, s = _cs1(center, scale)
+    return _np(D.transform_preds_batch(np.ascontiguousarray(co)[None], c, s, (int(output_size[0]), int(output_size[1]))))[0]
+
+
+def get_final_preds(config, batch_heatmaps, center, scale, output_flipped=None, flip_pairs=None):
+    """inference.py:149-186 -> (preds, maxvals, preds_in_input_space); dtypes as the reference
+    (float64 coordinates with TEST.POST_PROCESS in gaussian mode, float32 otherwise).
+
+    Extensions (both optional): `output_flipped` + `flip_pairs` fuse the flip test of
+    lib/core/function.py:154-171 (flip_back[_offset] + average) into the same launch, and
+    CUDA tensors are accepted for the heat maps, in which case nothing is copied to the host
+    except the three small results."""
+    if isinstance(batch_heatmaps, np.ndarray):
+        assert batch_heatmaps.ndim == 4, "batch_images should be 4-ndim"
+    c, s = _csN(center, scale)
+    tt = config.MODEL.TARGET_TYPE
+    if tt == "offset":
+        r = D.decode_offset(batch_heatmaps, c, s, float(config.LOSS.KPD), output_flipped, flip_pairs)
+    elif tt == "gaussian":
+        r = D.decode_gaussian(batch_heatmaps, c, s, output_flipped, flip_pairs,
+                              post_process=bool(config.TEST.POST_PROCESS))
+    else:
+        raise UnboundLocalError("local variable 'coords' referenced before assignment")  # what the reference does
+    return _np(r["preds"]), _np(r["maxvals"]), _np(r["preds_in"])
+
+
+def rsn_get_results(outputs, center, scale, output_flipped=None, flip_pairs=None):
+    """RSN prm decode glue (RSN/exps/RSN18.coco.e1.se.36x8x132000_prm/test.py:183-196):
+    outputs/255 -> get_max_preds -> post -> transform_preds; returns (preds f64 [B,K,2], maxvals [B,K,1])."""
+    c, s = _csN(center, scale)
+    r = D.decode_gaussian(outputs, c, s, output_flipped, flip_pairs, post_process=True, pre_div=255.0)
+    return _np(r["preds"]), _np(r["maxvals"])
+
+
+# --------------------------------------------------------------------------------- install
+def install(inference=None, transforms=None, joints_dataset=None):
+    """Substitute the CUDA codec into already-imported reference modules
+    (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset).  Returns a dict
+    {(module_name, attr): original} so the caller can undo it."""
+    saved = {}
+
+    def put(mod, name, fn):
+        if mod is None:
+            return
+        saved[(mod.__name__, name)] = getattr(mod, name, None)
+        setattr(mod, name, fn)
+
+    for nm in ("get_max_preds", "post", "get_final_preds", "transform_preds"):
+        put(inference, nm, globals()[nm])
+    for nm in ("flip_back", "flip_back_offset", "fliplr_joints", "transform_preds"):
+        put(transforms, nm, globals()[nm])
+    if joints_dataset is not None:
+        put(joints_dataset, "get_warpmatrix", get_warpmatrix)
+        put(joints_dataset, "rotate_points", rotate_points)
+        cls = joints_dataset.JointsDataset
+        saved[(joints_dataset.__name__, "JointsDataset.generate_target")] = cls.generate_target
+        cls.generate_target = JointsDataset.generate_target
+        cls.generate_target_batch = JointsDataset.generate_target_batch
+    return saved
+
