@@ -28,6 +28,34 @@ inline bool udp_force_generic()
 
 namespace udp {
 
+// Number of SMs of the current device (148 on B200), queried once per device.
+inline int sm_count()
+{
+    static int cached[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!cached[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+// Opt a persistent kernel into `smem` bytes of dynamic shared memory and return how many of its
+// CTAs fit on one SM.  0 on success, otherwise a cudaError_t.
+inline int persistent_grid(const void *kern, int threads, size_t smem, int *per_sm)
+{
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    int n = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, threads, smem);
+    if (e != cudaSuccess) return (int)e;
+    *per_sm = n < 1 ? 1 : n;
+    return 0;
+}
+
 constexpr double kPi = 3.141592653589793;  // math.pi
 
 // 16-byte streaming store: outputs are written once and never re-read by this library.

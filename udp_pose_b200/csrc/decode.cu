@@ -11,7 +11,7 @@
 //   get_final_preds (gaussian)     deep_hrnet/lib/core/inference.py:149-155,176-186
 //   transform_preds                deep_hrnet/lib/core/inference.py:20-27
 //   RSN prm glue (/255.0)          RSN/exps/RSN18.coco.e1.se.36x8x132000_prm/test.py:183-196
-#include "blur.cuh"
+#include "decode_pipe.cuh"
 
 namespace udp {
 
@@ -96,11 +96,79 @@ struct DecodeGaussArgs {
     float *blurred;
 };
 
+// Final stores of one map (thread 0): preds_in (:177-179), transform_preds, maxvals, index, packed.
 template <bool POST>
-__global__ void decode_gaussian_kernel(DecodeGaussArgs p)
+__device__ __forceinline__ void gauss_store(const DecodeGaussArgs &p, long long map, int n, double cx,
+                                            double cy, float bv, int bi)
+{
+    const int w = p.w, h = p.h;
+    double pin_x, pin_y, ox = cx, oy = cy;
+    if (POST) {  // :178-179 on a float64 array
+        pin_x = __dmul_rn(__ddiv_rn(cx, w - 1.0), 4 * w - 1.0);
+        pin_y = __dmul_rn(__ddiv_rn(cy, h - 1.0), 4 * h - 1.0);
+    } else {     // float32 array / python float
+        pin_x = (double)__fmul_rn(__fdiv_rn((float)cx, (float)(w - 1.0)), (float)(4 * w - 1.0));
+        pin_y = (double)__fmul_rn(__fdiv_rn((float)cy, (float)(h - 1.0)), (float)(4 * h - 1.0));
+    }
+    if (p.center) {
+        const CS cs = load_cs(p.center, p.scale, p.cs_f64, n);
+        transform_pred(cx, cy, cs, p.cs_f64, POST, w, h, ox, oy);
+    }
+    if (POST) {
+        double *pr = reinterpret_cast<double *>(p.preds) + map * 2;
+        pr[0] = ox; pr[1] = oy;
+        if (p.preds_in) { double *q = reinterpret_cast<double *>(p.preds_in) + map * 2; q[0] = pin_x; q[1] = pin_y; }
+    } else {
+        float *pr = reinterpret_cast<float *>(p.preds) + map * 2;
+        pr[0] = (float)ox; pr[1] = (float)oy;
+        if (p.preds_in) { float *q = reinterpret_cast<float *>(p.preds_in) + map * 2; q[0] = (float)pin_x; q[1] = (float)pin_y; }
+    }
+    p.maxvals[map] = bv;
+    if (p.argmax_idx) p.argmax_idx[map] = bi;
+    if (p.packed) { float *q = p.packed + map * 3; q[0] = (float)ox; q[1] = (float)oy; q[2] = bv; }
+}
+
+// The 7-tap Taylor (DARK-style) step of post() (:83-144), executed by one full warp: lane l < 7
+// supplies the blurred value of its tap through tapval(yy, xx) (coordinates already
+// edge-replicated).  Returns the refined coordinates in every lane.
+template <typename TapVal>
+__device__ __forceinline__ void taylor_step(int ix, int iy, int w, int h, float mn, float range,
+                                            float maxori, TapVal tapval, double &cx, double &cy)
+{
+    const int lane = threadIdx.x & 31;
+    const int tdy[7] = {0, 0, 0, 1, -1, 1, -1};
+    const int tdx[7] = {0, 1, -1, 0, 0, 1, -1};
+    double tap = 0.0;
+    if (lane < 7) {
+        const int yy = min(max(iy + tdy[lane], 0), h - 1), xx = min(max(ix + tdx[lane], 0), w - 1);
+        const float raw = tapval(yy, xx);
+        const float nv = __fmul_rn(__fdiv_rn(__fsub_rn(raw, mn), range), maxori);  // :79
+        tap = clip_log(nv);
+    }
+    const double I = __shfl_sync(0xffffffffu, tap, 0), Ix1 = __shfl_sync(0xffffffffu, tap, 1);
+    const double Ix1_ = __shfl_sync(0xffffffffu, tap, 2), Iy1 = __shfl_sync(0xffffffffu, tap, 3);
+    const double Iy1_ = __shfl_sync(0xffffffffu, tap, 4), Ix1y1 = __shfl_sync(0xffffffffu, tap, 5);
+    const double Ix1_y1_ = __shfl_sync(0xffffffffu, tap, 6);
+    const double dx = __dmul_rn(0.5, __dsub_rn(Ix1, Ix1_));
+    const double dy = __dmul_rn(0.5, __dsub_rn(Iy1, Iy1_));
+    const double dxx = __dadd_rn(__dsub_rn(Ix1, __dmul_rn(2.0, I)), Ix1_);
+    const double dyy = __dadd_rn(__dsub_rn(Iy1, __dmul_rn(2.0, I)), Iy1_);
+    double t = __dsub_rn(Ix1y1, Ix1);
+    t = __dsub_rn(t, Iy1); t = __dadd_rn(t, I); t = __dadd_rn(t, I);
+    t = __dsub_rn(t, Ix1_); t = __dsub_rn(t, Iy1_); t = __dadd_rn(t, Ix1_y1_);
+    const double dxy = __dmul_rn(0.5, t);
+    double inv[4];
+    inv2x2(dxx, dxy, dxy, dyy, inv);
+    cx = __dsub_rn((double)ix, __dadd_rn(__dmul_rn(inv[0], dx), __dmul_rn(inv[1], dy)));
+    cy = __dsub_rn((double)iy, __dadd_rn(__dmul_rn(inv[2], dx), __dmul_rn(inv[3], dy)));
+}
+
+// Generic path for one map: any (w, h) with w % 4 == 0, NaN-exact, optional blurred write-back.
+// Called by all threads of the CTA; smem must hold BlurGeom<3>::smem_floats(w, h) floats.
+template <bool POST>
+__device__ __noinline__ void decode_gauss_generic_map(const DecodeGaussArgs &p, float *smem, long long map)
 {
     constexpr int R = 3, L = 8;
-    extern __shared__ __align__(16) float smem[];
     __shared__ float red_v[32];
     __shared__ int red_i[32];
     __shared__ float red_mn[32], red_mx[32];
@@ -108,7 +176,6 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
     __shared__ float nb[9];
 
     const int w = p.w, h = p.h, hw = h * w;
-    const long long map = blockIdx.x;  // n*K + k
     const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
     float *A = smem;
     float *T = A + (size_t)h * BlurGeom<R>::stride_a(w);
@@ -180,62 +247,115 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
             }
         }
 
-        if (threadIdx.x < 32) {
-            // lanes 0..6: one stencil tap each (edge-replicated, :83-109)
-            const int tdy[7] = {0, 0, 0, 1, -1, 1, -1};
-            const int tdx[7] = {0, 1, -1, 0, 0, 1, -1};
-            double tap = 0.0;
-            if (lane < 7) {
-                const int yy = min(max(iy + tdy[lane], 0), h - 1), xx = min(max(ix + tdx[lane], 0), w - 1);
-                const float raw = nb[(yy - iy + 1) * 3 + (xx - ix + 1)];
-                const float nv = __fmul_rn(__fdiv_rn(__fsub_rn(raw, mn), range), maxori);  // :79
-                tap = clip_log(nv);
-            }
-            const double I = __shfl_sync(0xffffffffu, tap, 0), Ix1 = __shfl_sync(0xffffffffu, tap, 1);
-            const double Ix1_ = __shfl_sync(0xffffffffu, tap, 2), Iy1 = __shfl_sync(0xffffffffu, tap, 3);
-            const double Iy1_ = __shfl_sync(0xffffffffu, tap, 4), Ix1y1 = __shfl_sync(0xffffffffu, tap, 5);
-            const double Ix1_y1_ = __shfl_sync(0xffffffffu, tap, 6);
-            const double dx = __dmul_rn(0.5, __dsub_rn(Ix1, Ix1_));
-            const double dy = __dmul_rn(0.5, __dsub_rn(Iy1, Iy1_));
-            const double dxx = __dadd_rn(__dsub_rn(Ix1, __dmul_rn(2.0, I)), Ix1_);
-            const double dyy = __dadd_rn(__dsub_rn(Iy1, __dmul_rn(2.0, I)), Iy1_);
-            double t = __dsub_rn(Ix1y1, Ix1);
-            t = __dsub_rn(t, Iy1); t = __dadd_rn(t, I); t = __dadd_rn(t, I);
-            t = __dsub_rn(t, Ix1_); t = __dsub_rn(t, Iy1_); t = __dadd_rn(t, Ix1_y1_);
-            const double dxy = __dmul_rn(0.5, t);
-            double inv[4];
-            inv2x2(dxx, dxy, dxy, dyy, inv);
-            cx = __dsub_rn((double)ix, __dadd_rn(__dmul_rn(inv[0], dx), __dmul_rn(inv[1], dy)));
-            cy = __dsub_rn((double)iy, __dadd_rn(__dmul_rn(inv[2], dx), __dmul_rn(inv[3], dy)));
-        }
+        if (threadIdx.x < 32)
+            taylor_step(ix, iy, w, h, mn, range, maxori,
+                        [&](int yy, int xx) { return nb[(yy - iy + 1) * 3 + (xx - ix + 1)]; }, cx, cy);
     }
 
-    if (threadIdx.x == 0) {
-        double pin_x, pin_y, ox = cx, oy = cy;
-        if (POST) {  // :178-179 on a float64 array
-            pin_x = __dmul_rn(__ddiv_rn(cx, w - 1.0), 4 * w - 1.0);
-            pin_y = __dmul_rn(__ddiv_rn(cy, h - 1.0), 4 * h - 1.0);
-        } else {     // float32 array / python float
-            pin_x = (double)__fmul_rn(__fdiv_rn((float)cx, (float)(w - 1.0)), (float)(4 * w - 1.0));
-            pin_y = (double)__fmul_rn(__fdiv_rn((float)cy, (float)(h - 1.0)), (float)(4 * h - 1.0));
+    if (threadIdx.x == 0) gauss_store<POST>(p, map, n, cx, cy, bv, bi);
+    __syncthreads();  // the static scratch above may be reused by the caller's next map
+}
+
+template <bool POST>
+__global__ void decode_gaussian_kernel(DecodeGaussArgs p)
+{
+    extern __shared__ __align__(16) float smem[];
+    decode_gauss_generic_map<POST>(p, smem, blockIdx.x);
+}
+
+// ---------------------------------------------------------------------------------------
+// Streaming fast path (decode_pipe.cuh): persistent CTAs, 2-stage cp.async pipeline.
+// ---------------------------------------------------------------------------------------
+template <int W, int H, int NT, bool POST, bool DIV255>
+__global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArgs p, long long maps)
+{
+    constexpr int R = 3;
+    using G = PipeGeom<W, H, R, NT>;
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float s_wmax[G::NWARP], s_mn[G::NWARP], s_mx[G::NWARP];
+    __shared__ int s_idx;
+    constexpr int hw = H * W;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
+    const bool has_fl = p.hm_flipped != nullptr;
+
+    auto src_of = [&](long long m) { return p.hm + m * (long long)hw; };
+    auto fl_of = [&](long long m) -> const float * {
+        if (!has_fl) return nullptr;
+        const long long n = m / p.K;
+        const int k = (int)(m - n * p.K);
+        return p.hm_flipped + (n * p.K + p.flip_perm[k]) * (long long)hw;
+    };
+
+    long long map = blockIdx.x;
+    int s = 0;
+    if (map < maps) pipe_prefetch<W, H, R, NT>(smem, src_of(map), fl_of(map));
+    cp_async_commit();
+    for (; map < maps; map += gridDim.x, s ^= 1) {
+        float *stage = smem + s * G::STAGE;
+        cp_async_wait_all();
+        __syncthreads();  // (A) this map has landed; the previous map's T is dead
+        const long long next = map + gridDim.x;
+        if (next < maps) pipe_prefetch<W, H, R, NT>(smem + (s ^ 1) * G::STAGE, src_of(next), fl_of(next));
+        cp_async_commit();
+        if (threadIdx.x == 0) s_idx = 0x7fffffff;
+
+        float2 v[G::NCOL];
+        pipe_window<W, H, R, NT, DIV255>(stage, has_fl, pr, xs, v);
+        float2 fs;
+        const float lm = pipe_local_max<W, H, R, NT>(v, fs);
+        float wm = lm;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+        if (lane == 0) s_wmax[warp] = wm;
+        const bool bad = !(fabsf(fs.x + fs.y) < INFINITY);
+        if (__syncthreads_or(bad)) {  // (B') a non-finite value: NaN-exact generic path for this map
+            cp_async_wait_all();
+            __syncthreads();
+            decode_gauss_generic_map<POST>(p, smem, map);
+            if (next < maps) pipe_prefetch<W, H, R, NT>(smem + (s ^ 1) * G::STAGE, src_of(next), fl_of(next));
+            cp_async_commit();
+            continue;
         }
-        if (p.center) {
-            const CS cs = load_cs(p.center, p.scale, p.cs_f64, n);
-            transform_pred(cx, cy, cs, p.cs_f64, POST, w, h, ox, oy);
-        }
+        // (B) the raw stage is consumed (T may overwrite it) and the warp maxima are published
+        float M = s_wmax[0];
+#pragma unroll
+        for (int q = 1; q < G::NWARP; ++q) M = fmaxf(M, s_wmax[q]);
+        if (lm == M) atomicMin(&s_idx, pipe_first_index<W, H, R, NT>(v, M, pr, xs));
+        float *T = stage;
+        if (POST) pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
+        __syncthreads();  // (C) T complete, s_idx final
+        const int bi = s_idx;
+        const float bv = M;
+        const bool mask = bv > 0.0f;
+        const int ix = mask ? bi % W : 0, iy = mask ? bi / W : 0;
+        const int n = (int)(map / p.K);
+        double cx = (double)ix, cy = (double)iy;
         if (POST) {
-            double *pr = reinterpret_cast<double *>(p.preds) + map * 2;
-            pr[0] = ox; pr[1] = oy;
-            if (p.preds_in) { double *q = reinterpret_cast<double *>(p.preds_in) + map * 2; q[0] = pin_x; q[1] = pin_y; }
-        } else {
-            float *pr = reinterpret_cast<float *>(p.preds) + map * 2;
-            pr[0] = (float)ox; pr[1] = (float)oy;
-            if (p.preds_in) { float *q = reinterpret_cast<float *>(p.preds_in) + map * 2; q[0] = (float)pin_x; q[1] = (float)pin_y; }
+            float mn = INFINITY, mx = -INFINITY;
+            pipe_col_pass<W, H, R, NT>(T, [&](int, int, float2 sv) {
+                mn = fmin3(mn, sv.x, sv.y);
+                mx = fmax3(mx, sv.x, sv.y);
+            });
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            }
+            if (lane == 0) { s_mn[warp] = mn; s_mx[warp] = mx; }
+            __syncthreads();  // (D)
+            if (warp == 0) {
+                mn = s_mn[0]; mx = s_mx[0];
+#pragma unroll
+                for (int q = 1; q < G::NWARP; ++q) { mn = fminf(mn, s_mn[q]); mx = fmaxf(mx, s_mx[q]); }
+                const float range = __fsub_rn(mx, mn);
+                taylor_step(ix, iy, W, H, mn, range, bv,
+                            [&](int yy, int xx) { return pipe_col_at<W, H, R, NT>(T, yy, xx); }, cx, cy);
+            }
         }
-        p.maxvals[map] = bv;
-        if (p.argmax_idx) p.argmax_idx[map] = bi;
-        if (p.packed) { float *q = p.packed + map * 3; q[0] = (float)ox; q[1] = (float)oy; q[2] = bv; }
+        if (threadIdx.x == 0) gauss_store<POST>(p, map, n, cx, cy, bv, bi);
     }
+    cp_async_wait_all();
 }
 
 }  // namespace udp
@@ -268,15 +388,42 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
     if (blurred && !post_process) return UDP_EINVAL;
     udp::DecodeGaussArgs a{hm, hm_flipped, flip_perm, center, scale, cs_f64, pre_div, K, w, h,
                            preds, maxvals, preds_in, argmax_idx, packed, blurred};
-    size_t smem = udp::BlurGeom<3>::smem_floats(w, h) * sizeof(float);
-    if (smem > 200 * 1024) return UDP_EINVAL;
-    auto kern = post_process ? udp::decode_gaussian_kernel<true> : udp::decode_gaussian_kernel<false>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    const int threads = (h * w <= 4096) ? 128 : 256;
     long long maps = (long long)N * K;
     if (maps > 0x7fffffffLL) return UDP_EINVAL;
-    kern<<<(unsigned)maps, threads, smem, (cudaStream_t)stream>>>(a);
+    size_t gsmem = udp::BlurGeom<3>::smem_floats(w, h) * sizeof(float);
+    if (gsmem > 200 * 1024) return UDP_EINVAL;
+
+    // Streaming fast path: the reference's map shapes, plain or /255 (RSN) pre-scaling, no
+    // blurred write-back.  Everything else (and every map holding a NaN/inf) runs the generic code.
+    if (!udp_force_generic() && !blurred && (pre_div == 0.0f || pre_div == 255.0f)) {
+#define UDP_GAUSS_PIPE(WW, HH, NT)                                                               \
+        if (w == WW && h == HH) {                                                                \
+            using G = udp::PipeGeom<WW, HH, 3, NT>;                                              \
+            const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
+            void (*kern)(udp::DecodeGaussArgs, long long) =                                      \
+                post_process ? (pre_div != 0.0f ? udp::decode_gaussian_pipe_kernel<WW, HH, NT, true, true>   \
+                                                : udp::decode_gaussian_pipe_kernel<WW, HH, NT, true, false>) \
+                             : (pre_div != 0.0f ? udp::decode_gaussian_pipe_kernel<WW, HH, NT, false, true>  \
+                                                : udp::decode_gaussian_pipe_kernel<WW, HH, NT, false, false>); \
+            int per_sm = 0;                                                                      \
+            int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
+            if (rc) return rc;                                                                   \
+            long long grid = (long long)per_sm * udp::sm_count();                                \
+            if (grid > maps) grid = maps;                                                        \
+            kern<<<(unsigned)grid, NT, smem, (cudaStream_t)stream>>>(a, maps);                   \
+            UDP_LAUNCH_CHECK();                                                                  \
+            return 0;                                                                            \
+        }
+        UDP_GAUSS_PIPE(48, 64, 96)
+        UDP_GAUSS_PIPE(64, 64, 128)
+        UDP_GAUSS_PIPE(72, 96, 288)
+#undef UDP_GAUSS_PIPE
+    }
+    auto kern = post_process ? udp::decode_gaussian_kernel<true> : udp::decode_gaussian_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);
+    if (e != cudaSuccess) return (int)e;
+    const int threads = (h * w <= 4096) ? 128 : 256;
+    kern<<<(unsigned)maps, threads, gsmem, (cudaStream_t)stream>>>(a);
     UDP_LAUNCH_CHECK();
     return 0;
 }

@@ -1,0 +1,249 @@
+// decode_pipe.cuh -- the streaming skeleton shared by both fused decoders (second generation).
+//
+// What the first-generation kernels got wrong (ncu, profiles/r01_decode_gauss_v1_ncu.txt and
+// profiles/r01_decode_offset_fast_ncu.txt): one CTA per map with load -> sync -> blur -> sync
+// phases left HBM idle while a CTA computed and the SM idle while it loaded (17-27 % occupancy,
+// 36-48 % issue-active, 20-30 % of DRAM peak), and ~8000 warp-instructions per 64x48 map.
+//
+// This version:
+//  * persistent CTAs (a few per SM) walk the (person, joint) maps with a 2-stage cp.async
+//    pipeline: while map i is being decoded, the 16-byte asynchronous copies of map i+1 (and
+//    of its mirrored partner map) are already in flight into the other stage.  The copies
+//    place each row at a padded stride (SR/4 odd) so that the later per-row LDS.128 reads are
+//    bank-conflict free; no thread ever holds HBM data in registers while waiting.
+//  * the flip test ((out + mirror(partner)) * 0.5, utils/transforms.py:15-47 +
+//    core/function.py:171) is fused into the ROW pass: a thread owns two rows (p, p + H/2) and a
+//    column segment, averages its window straight into row-paired registers and runs cv2's
+//    left-to-right FMA chain with packed fma.rn.f32x2 -- the padded copy A2 of the first
+//    generation, its store/load round trip and one barrier are gone.
+//  * T (the row-pass result, with reflected halo rows) aliases the stage the map came from,
+//    so shared memory is just the two stages.
+//  * the column pass pairs two COLUMNS (x, x+1), cv2's centre-then-symmetric-pairs order.
+//  * the raw arg-max needs only FMNMX per element: block max first, then the (rare) threads
+//    whose local max equals it rescan their registers for the first index.
+// Arithmetic and summation order are unchanged: results stay bit-identical.
+// Maps holding a non-finite value are handed to the generic, NaN-exact code path.
+#pragma once
+#include "blur_fast.cuh"
+
+namespace udp {
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+__device__ __forceinline__ float fmax3(float a, float b, float c)
+{
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ float fmin3(float a, float b, float c)
+{
+    float d;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// x / 255.0f, correctly rounded, without the division sequence: q = x*y, one FMA residual,
+// one FMA correction (y = RN(1/255)).  Checked exhaustively against x / 255.0f for every
+// finite float32 (only -0.0 needed the select).
+__device__ __forceinline__ float div255(float x)
+{
+    const float y = 0x1.010102p-8f;
+    const float q = __fmul_rn(x, y);
+    const float r = fmaf(-q, 255.0f, x);
+    const float q2 = fmaf(r, y, q);
+    return x == 0.0f ? x : q2;
+}
+
+template <int W, int H, int R, int NT>
+struct PipeGeom {
+    static_assert(W % 4 == 0 && H % 2 == 0, "map shape");
+    static constexpr int PAD = (R <= 4) ? 4 : 8;          // halo columns loaded per side (float4 units)
+    static constexpr int HP = H / 2;                      // thread rows: (p, p + HP)
+    static_assert(NT % HP == 0, "NT must be a multiple of H/2");
+    static constexpr int XS = NT / HP;                    // column segments
+    static_assert(W % XS == 0, "row-pass split");
+    static constexpr int SEG = W / XS;
+    static_assert(SEG % 4 == 0 && SEG >= R + 1, "segment");
+    static constexpr int NCOL = SEG + 2 * PAD;            // window columns per row
+    static constexpr int NV4 = NCOL / 4;
+    static constexpr int CP = W / 2;                      // column pairs
+    static_assert(NT % CP == 0, "NT must be a multiple of W/2");
+    static constexpr int YS = NT / CP;
+    static_assert(H % YS == 0, "column-pass split");
+    static constexpr int RS = H / YS;
+    static constexpr int SR = (W / 4) % 2 == 1 ? W : W + 4;  // raw row stride, SR/4 odd
+    static constexpr int ST = W + 2;                      // T row stride
+    static constexpr int TROWS = H + 2 * R;
+    static constexpr int RAW = H * SR;                    // floats per raw tensor
+    static constexpr int STAGE = (2 * RAW > TROWS * ST) ? 2 * RAW : ((TROWS * ST + 3) / 4) * 4;
+    static constexpr size_t SMEM = (size_t)2 * STAGE * sizeof(float);
+    static constexpr int NWARP = (NT + 31) / 32;
+};
+
+// Asynchronous copy of one map (and its flip partner) into a stage, rows at stride SR.
+template <int W, int H, int R, int NT>
+__device__ __forceinline__ void pipe_prefetch(float *stage, const float *__restrict__ src,
+                                              const float *__restrict__ fl)
+{
+    using G = PipeGeom<W, H, R, NT>;
+    constexpr int W4 = W / 4, ITEMS = H * W4;
+#pragma unroll
+    for (int it0 = 0; it0 < ITEMS; it0 += NT) {
+        const int it = it0 + threadIdx.x;
+        if (ITEMS % NT == 0 || it < ITEMS) {
+            const int y = it / W4, x = (it - y * W4) << 2;
+            cp_async16(stage + y * G::SR + x, src + it * 4);
+            if (fl) cp_async16(stage + G::RAW + y * G::SR + x, fl + it * 4);
+        }
+    }
+}
+
+// The averaged window of one thread: v[j] = (row p, row p + HP) at column x0 - PAD + j.
+// mode: 0 = no flip, 1 = flip (+), 2 = flip with the partner negated (x-offset channels).
+template <int W, int H, int R, int NT, bool DIV255>
+__device__ __forceinline__ void pipe_window(const float *stage, bool has_fl, int p, int xs,
+                                            float2 (&v)[PipeGeom<W, H, R, NT>::NCOL])
+{
+    using G = PipeGeom<W, H, R, NT>;
+    constexpr int PAD = G::PAD, SEG = G::SEG;
+    const int x0 = xs * SEG;
+    const float *a0 = stage + p * G::SR, *a1 = a0 + G::HP * G::SR;
+    const float *f0 = a0 + G::RAW, *f1 = a1 + G::RAW;
+#pragma unroll
+    for (int q = 0; q < G::NV4; ++q) {
+        int xc = x0 - PAD + 4 * q;
+        xc = xc < 0 ? 0 : (xc > W - 4 ? W - 4 : xc);  // out-of-map chunks are replaced below
+        const float4 r0 = *reinterpret_cast<const float4 *>(a0 + xc);
+        const float4 r1 = *reinterpret_cast<const float4 *>(a1 + xc);
+        float2 t0 = make_float2(r0.x, r1.x), t1 = make_float2(r0.y, r1.y);
+        float2 t2 = make_float2(r0.z, r1.z), t3 = make_float2(r0.w, r1.w);
+        if (has_fl) {
+            const float4 g0 = *reinterpret_cast<const float4 *>(f0 + (W - 4 - xc));
+            const float4 g1 = *reinterpret_cast<const float4 *>(f1 + (W - 4 - xc));
+            t0.x = __fmul_rn(__fadd_rn(r0.x, g0.w), 0.5f); t0.y = __fmul_rn(__fadd_rn(r1.x, g1.w), 0.5f);
+            t1.x = __fmul_rn(__fadd_rn(r0.y, g0.z), 0.5f); t1.y = __fmul_rn(__fadd_rn(r1.y, g1.z), 0.5f);
+            t2.x = __fmul_rn(__fadd_rn(r0.z, g0.y), 0.5f); t2.y = __fmul_rn(__fadd_rn(r1.z, g1.y), 0.5f);
+            t3.x = __fmul_rn(__fadd_rn(r0.w, g0.x), 0.5f); t3.y = __fmul_rn(__fadd_rn(r1.w, g1.x), 0.5f);
+        }
+        if (DIV255) {
+            t0.x = div255(t0.x); t0.y = div255(t0.y); t1.x = div255(t1.x); t1.y = div255(t1.y);
+            t2.x = div255(t2.x); t2.y = div255(t2.y); t3.x = div255(t3.x); t3.y = div255(t3.y);
+        }
+        v[4 * q] = t0; v[4 * q + 1] = t1; v[4 * q + 2] = t2; v[4 * q + 3] = t3;
+    }
+    // reflect-101 columns at the map borders: column -1-i <- column 1+i, column W+i <- column W-2-i
+    if (xs == 0) {
+#pragma unroll
+        for (int i = 0; i < R; ++i) v[PAD - 1 - i] = v[PAD + 1 + i];
+    }
+    if (xs == G::XS - 1) {
+#pragma unroll
+        for (int i = 0; i < R; ++i) v[PAD + SEG + i] = v[PAD + SEG - 2 - i];
+    }
+}
+
+// Row filter from the register window into T (stride ST, R halo rows above and below).
+template <int W, int H, int R, int NT>
+__device__ __forceinline__ void pipe_row_filter(const float2 (&v)[PipeGeom<W, H, R, NT>::NCOL],
+                                                float *T, int p, int xs)
+{
+    using G = PipeGeom<W, H, R, NT>;
+    constexpr int PAD = G::PAD, SEG = G::SEG;
+    const int x0 = xs * SEG, y0 = p, y1 = p + G::HP;
+    float *t0 = T + (y0 + R) * G::ST + x0, *t1 = T + (y1 + R) * G::ST + x0;
+    // reflected halo rows: T row -r = row r (1..R) is owned by y0 = r; row H-1+r = row H-1-r by y1
+    const bool top = (y0 >= 1 && y0 <= R), bot = (y1 >= H - 1 - R && y1 <= H - 2);
+    float *h0 = T + (R - y0) * G::ST + x0;
+    float *h1 = T + (2 * (H - 1) - y1 + R) * G::ST + x0;
+#pragma unroll
+    for (int o = 0; o < SEG; o += 2) {
+        float2 s0 = fmul2(v[PAD - R + o], Taps<R>::k(0)), s1 = fmul2(v[PAD - R + o + 1], Taps<R>::k(0));
+#pragma unroll
+        for (int i = 1; i < 2 * R + 1; ++i) {
+            s0 = ffma2(v[PAD - R + o + i], Taps<R>::k(i), s0);
+            s1 = ffma2(v[PAD - R + o + 1 + i], Taps<R>::k(i), s1);
+        }
+        const float2 ra = make_float2(s0.x, s1.x), rb = make_float2(s0.y, s1.y);
+        *reinterpret_cast<float2 *>(t0 + o) = ra;
+        *reinterpret_cast<float2 *>(t1 + o) = rb;
+        if (top) *reinterpret_cast<float2 *>(h0 + o) = ra;
+        if (bot) *reinterpret_cast<float2 *>(h1 + o) = rb;
+    }
+}
+
+// Column pass: thread = (column pair c, y segment); emit(y, x, float2) gets blurred (y,x),(y,x+1).
+template <int W, int H, int R, int NT, typename Emit>
+__device__ __forceinline__ void pipe_col_pass(const float *T, Emit emit)
+{
+    using G = PipeGeom<W, H, R, NT>;
+    constexpr int RS = G::RS;
+    const int c = threadIdx.x % G::CP, ys = threadIdx.x / G::CP;
+    const float *base = T + (ys * RS) * G::ST + 2 * c;
+    float2 t[RS + 2 * R];
+#pragma unroll
+    for (int i = 0; i < RS + 2 * R; ++i) t[i] = *reinterpret_cast<const float2 *>(base + i * G::ST);
+#pragma unroll
+    for (int o = 0; o < RS; ++o) {
+        float2 s = ffma2(t[o + R], Taps<R>::k(R), make_float2(0.f, 0.f));
+#pragma unroll
+        for (int i = 1; i <= R; ++i) s = ffma2(fadd2(t[o + R + i], t[o + R - i]), Taps<R>::k(R + i), s);
+        emit(ys * RS + o, 2 * c, s);
+    }
+}
+
+// One blurred value from T (same order as the column pass).
+template <int W, int H, int R, int NT>
+__device__ __forceinline__ float pipe_col_at(const float *T, int y, int x)
+{
+    using G = PipeGeom<W, H, R, NT>;
+    const float *q = T + (y + R) * G::ST + x;
+    float s = fmaf(q[0], Taps<R>::k(R), 0.0f);
+#pragma unroll
+    for (int i = 1; i <= R; ++i) s = fmaf(__fadd_rn(q[i * G::ST], q[-i * G::ST]), Taps<R>::k(R + i), s);
+    return s;
+}
+
+// Raw first-index arg-max over the thread's own SEG columns of its two rows.
+// Step 1: local maxima (FMNMX only).  Step 2 (after the block max M is known): first index == M.
+template <int W, int H, int R, int NT>
+__device__ __forceinline__ float pipe_local_max(const float2 (&v)[PipeGeom<W, H, R, NT>::NCOL], float2 &fsum)
+{
+    using G = PipeGeom<W, H, R, NT>;
+    float m0 = -INFINITY, m1 = -INFINITY;
+    float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = G::PAD; j < G::PAD + G::SEG; j += 2) {
+        m0 = fmax3(m0, v[j].x, v[j + 1].x);
+        m1 = fmax3(m1, v[j].y, v[j + 1].y);
+        acc = fadd2(acc, fadd2(v[j], v[j + 1]));
+    }
+    fsum = acc;
+    return fmaxf(m0, m1);
+}
+
+template <int W, int H, int R, int NT>
+__device__ __forceinline__ int pipe_first_index(const float2 (&v)[PipeGeom<W, H, R, NT>::NCOL], float M,
+                                                int p, int xs)
+{
+    using G = PipeGeom<W, H, R, NT>;
+    int best = 0x7fffffff;
+    const int b0 = p * W + xs * G::SEG, b1 = b0 + G::HP * W;
+#pragma unroll
+    for (int j = G::SEG - 1; j >= 0; --j) {  // descending, so the lowest index is written last
+        if (v[G::PAD + j].y == M) best = b1 + j;
+    }
+#pragma unroll
+    for (int j = G::SEG - 1; j >= 0; --j) {
+        if (v[G::PAD + j].x == M) best = b0 + j;
+    }
+    return best;
+}
+
+}  // namespace udp
