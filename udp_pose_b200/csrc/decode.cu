@@ -163,6 +163,29 @@ __device__ __forceinline__ void taylor_step(int ix, int iy, int w, int h, float 
     cy = __dsub_rn((double)iy, __dadd_rn(__dmul_rn(inv[2], dx), __dmul_rn(inv[3], dy)));
 }
 
+// The same step done by ONE thread from the seven blurred tap values (order: centre, x+1, x-1,
+// y+1, y-1, (x+1,y+1), (x-1,y-1)); used by the batched tail of the streaming kernel.
+__device__ __forceinline__ void taylor_scalar(const float *tap, int ix, int iy, float mn, float range,
+                                              float maxori, double &cx, double &cy)
+{
+    double I[7];
+#pragma unroll
+    for (int t = 0; t < 7; ++t)
+        I[t] = clip_log(__fmul_rn(__fdiv_rn(__fsub_rn(tap[t], mn), range), maxori));  // :79, :81-82
+    const double dx = __dmul_rn(0.5, __dsub_rn(I[1], I[2]));
+    const double dy = __dmul_rn(0.5, __dsub_rn(I[3], I[4]));
+    const double dxx = __dadd_rn(__dsub_rn(I[1], __dmul_rn(2.0, I[0])), I[2]);
+    const double dyy = __dadd_rn(__dsub_rn(I[3], __dmul_rn(2.0, I[0])), I[4]);
+    double t = __dsub_rn(I[5], I[1]);
+    t = __dsub_rn(t, I[3]); t = __dadd_rn(t, I[0]); t = __dadd_rn(t, I[0]);
+    t = __dsub_rn(t, I[2]); t = __dsub_rn(t, I[4]); t = __dadd_rn(t, I[6]);
+    const double dxy = __dmul_rn(0.5, t);
+    double inv[4];
+    inv2x2(dxx, dxy, dxy, dyy, inv);
+    cx = __dsub_rn((double)ix, __dadd_rn(__dmul_rn(inv[0], dx), __dmul_rn(inv[1], dy)));
+    cy = __dsub_rn((double)iy, __dadd_rn(__dmul_rn(inv[2], dx), __dmul_rn(inv[3], dy)));
+}
+
 // Generic path for one map: any (w, h) with w % 4 == 0, NaN-exact, optional blurred write-back.
 // Called by all threads of the CTA; smem must hold BlurGeom<3>::smem_floats(w, h) floats.
 template <bool POST>
@@ -266,18 +289,30 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
 // ---------------------------------------------------------------------------------------
 // Streaming fast path (decode_pipe.cuh): persistent CTAs, 2-stage cp.async pipeline.
 // ---------------------------------------------------------------------------------------
-template <int W, int H, int NT, bool POST, bool DIV255>
+// Per map only three barriers remain: (A) data landed, (B) raw stage consumed / warp maxima
+// published, (C) T complete.  Everything that is serial per map -- min/max combine, the float64
+// log + Taylor + 2x2 solve, the inverse affine and the result stores -- is deferred: each map
+// leaves 7 tap values, per-warp min/max, maxval and index in a shared-memory mailbox, and every 32
+// maps the 32 lanes of one warp finish one mailbox entry each (first build: that tail ran on 7
+// lanes per map while the other warps waited at the next barrier -- 37 % of stall samples were
+// barrier stalls, 19 % of all instructions were the tail).
+template <int W, int H, int NT, bool POST, bool FLIP, bool DIV255>
 __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArgs p, long long maps)
 {
     constexpr int R = 3;
     using G = PipeGeom<W, H, R, NT>;
+    constexpr int NW = G::NWARP;
+    constexpr int B_MN = 7, B_MX = 7 + NW, B_BV = 7 + 2 * NW, B_BI = B_BV + 1, B_MAP = B_BV + 2;
+    constexpr int BOXW = ((B_MAP + 1) | 1);  // odd stride: conflict-free entry-per-thread reads
     extern __shared__ __align__(16) float smem[];
-    __shared__ float s_wmax[G::NWARP], s_mn[G::NWARP], s_mx[G::NWARP];
+    __shared__ float s_wmax[NW];
     __shared__ int s_idx;
+    constexpr int NBOX = 32;
+    __shared__ float s_box[NBOX * BOXW];
     constexpr int hw = H * W;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
-    const bool has_fl = p.hm_flipped != nullptr;
+    constexpr bool has_fl = FLIP;
 
     auto src_of = [&](long long m) { return p.hm + m * (long long)hw; };
     auto fl_of = [&](long long m) -> const float * {
@@ -286,9 +321,27 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
         const int k = (int)(m - n * p.K);
         return p.hm_flipped + (n * p.K + p.flip_perm[k]) * (long long)hw;
     };
+    auto flush = [&](int count) {  // executed by one full warp
+        if (lane < count) {
+            const float *b = s_box + lane * BOXW;
+            const float bv = b[B_BV];
+            const int bi = __float_as_int(b[B_BI]);
+            const long long map = __float_as_int(b[B_MAP]);
+            const bool mask = bv > 0.0f;
+            const int ix = mask ? bi % W : 0, iy = mask ? bi / W : 0;
+            double cx = (double)ix, cy = (double)iy;
+            if (POST) {
+                float mn = b[B_MN], mx = b[B_MX];
+#pragma unroll
+                for (int q = 1; q < NW; ++q) { mn = fminf(mn, b[B_MN + q]); mx = fmaxf(mx, b[B_MX + q]); }
+                taylor_scalar(b, ix, iy, mn, __fsub_rn(mx, mn), bv, cx, cy);
+            }
+            gauss_store<POST>(p, map, (int)(map / p.K), cx, cy, bv, bi);
+        }
+    };
 
     long long map = blockIdx.x;
-    int s = 0;
+    int s = 0, slot = 0;
     if (map < maps) pipe_prefetch<W, H, R, NT>(smem, src_of(map), fl_of(map));
     cp_async_commit();
     for (; map < maps; map += gridDim.x, s ^= 1) {
@@ -299,17 +352,23 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
         if (next < maps) pipe_prefetch<W, H, R, NT>(smem + (s ^ 1) * G::STAGE, src_of(next), fl_of(next));
         cp_async_commit();
         if (threadIdx.x == 0) s_idx = 0x7fffffff;
+        // mailbox full: one warp finishes the 32 queued maps.  No extra barrier: the next mailbox
+        // write comes after barrier (C) of this iteration, which this warp has to pass too.
+        if (slot == NBOX) {
+            if (warp == 0) flush(NBOX);
+            slot = 0;
+        }
 
-        float2 v[G::NCOL];
-        pipe_window<W, H, R, NT, DIV255>(stage, has_fl, pr, xs, v);
-        float2 fs;
+        f32x2 v[G::NCOL];
+        pipe_window<W, H, R, NT, FLIP, DIV255>(stage, pr, xs, v);
+        float fs;
         const float lm = pipe_local_max<W, H, R, NT>(v, fs);
         float wm = lm;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
         if (lane == 0) s_wmax[warp] = wm;
-        const bool bad = !(fabsf(fs.x + fs.y) < INFINITY);
-        if (__syncthreads_or(bad)) {  // (B') a non-finite value: NaN-exact generic path for this map
+        const bool bad = !(fabsf(fs) < INFINITY);
+        if (__syncthreads_or(bad)) {  // a non-finite value: NaN-exact generic path for this map
             cp_async_wait_all();
             __syncthreads();
             decode_gauss_generic_map<POST>(p, smem, map);
@@ -320,42 +379,54 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
         // (B) the raw stage is consumed (T may overwrite it) and the warp maxima are published
         float M = s_wmax[0];
 #pragma unroll
-        for (int q = 1; q < G::NWARP; ++q) M = fmaxf(M, s_wmax[q]);
+        for (int q = 1; q < NW; ++q) M = fmaxf(M, s_wmax[q]);
         if (lm == M) atomicMin(&s_idx, pipe_first_index<W, H, R, NT>(v, M, pr, xs));
         float *T = stage;
         if (POST) pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
         __syncthreads();  // (C) T complete, s_idx final
+        float *box = s_box + slot * BOXW;
         const int bi = s_idx;
-        const float bv = M;
-        const bool mask = bv > 0.0f;
-        const int ix = mask ? bi % W : 0, iy = mask ? bi / W : 0;
-        const int n = (int)(map / p.K);
-        double cx = (double)ix, cy = (double)iy;
         if (POST) {
+            if (warp == NW - 1 && lane < 7) {  // the seven taps of the Taylor step (:100-109), edge-replicated
+                const int tdy[7] = {0, 0, 0, 1, -1, 1, -1};
+                const int tdx[7] = {0, 1, -1, 0, 0, 1, -1};
+                const bool mask = M > 0.0f;
+                const int ix = mask ? bi % W : 0, iy = mask ? bi / W : 0;
+                const int yy = min(max(iy + tdy[lane], 0), H - 1), xx = min(max(ix + tdx[lane], 0), W - 1);
+                box[lane] = pipe_col_at<W, H, R, NT>(T, yy, xx);
+            }
             float mn = INFINITY, mx = -INFINITY;
-            pipe_col_pass<W, H, R, NT>(T, [&](int, int, float2 sv) {
-                mn = fmin3(mn, sv.x, sv.y);
-                mx = fmax3(mx, sv.x, sv.y);
+            pipe_col_pass<W, H, R, NT>(T, [&](int, int, float a, float b) {
+                mn = fmin3(mn, a, b);
+                mx = fmax3(mx, a, b);
             });
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
                 mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
             }
-            if (lane == 0) { s_mn[warp] = mn; s_mx[warp] = mx; }
-            __syncthreads();  // (D)
-            if (warp == 0) {
-                mn = s_mn[0]; mx = s_mx[0];
-#pragma unroll
-                for (int q = 1; q < G::NWARP; ++q) { mn = fminf(mn, s_mn[q]); mx = fmaxf(mx, s_mx[q]); }
-                const float range = __fsub_rn(mx, mn);
-                taylor_step(ix, iy, W, H, mn, range, bv,
-                            [&](int yy, int xx) { return pipe_col_at<W, H, R, NT>(T, yy, xx); }, cx, cy);
-            }
+            if (lane == 0) { box[B_MN + warp] = mn; box[B_MX + warp] = mx; }
         }
-        if (threadIdx.x == 0) gauss_store<POST>(p, map, n, cx, cy, bv, bi);
+        if (threadIdx.x == 0) {
+            box[B_BV] = M;
+            box[B_BI] = __int_as_float(bi);
+            box[B_MAP] = __int_as_float((int)map);
+        }
+        ++slot;
     }
     cp_async_wait_all();
+    __syncthreads();
+    if (slot && warp == 0) flush(slot);
+}
+
+template <int W, int H, int NT>
+static void (*pick_gauss_pipe(bool post, bool flip, bool div))(DecodeGaussArgs, long long)
+{
+#define UDP_PICK(P, F, D) if (post == P && flip == F && div == D) return decode_gaussian_pipe_kernel<W, H, NT, P, F, D>;
+    UDP_PICK(true, true, false) UDP_PICK(true, false, false) UDP_PICK(true, true, true) UDP_PICK(true, false, true)
+    UDP_PICK(false, true, false) UDP_PICK(false, false, false) UDP_PICK(false, true, true)
+#undef UDP_PICK
+    return decode_gaussian_pipe_kernel<W, H, NT, false, false, true>;
 }
 
 }  // namespace udp
@@ -400,11 +471,8 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
         if (w == WW && h == HH) {                                                                \
             using G = udp::PipeGeom<WW, HH, 3, NT>;                                              \
             const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
-            void (*kern)(udp::DecodeGaussArgs, long long) =                                      \
-                post_process ? (pre_div != 0.0f ? udp::decode_gaussian_pipe_kernel<WW, HH, NT, true, true>   \
-                                                : udp::decode_gaussian_pipe_kernel<WW, HH, NT, true, false>) \
-                             : (pre_div != 0.0f ? udp::decode_gaussian_pipe_kernel<WW, HH, NT, false, true>  \
-                                                : udp::decode_gaussian_pipe_kernel<WW, HH, NT, false, false>); \
+            void (*kern)(udp::DecodeGaussArgs, long long) = udp::pick_gauss_pipe<WW, HH, NT>(            \
+                post_process != 0, hm_flipped != nullptr, pre_div != 0.0f);                      \
             int per_sm = 0;                                                                      \
             int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
             if (rc) return rc;                                                                   \

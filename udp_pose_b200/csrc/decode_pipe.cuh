@@ -36,6 +36,47 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
+// Packed fp32x2 values live in 64-bit registers from the moment they are formed, so ptxas keeps
+// them as aligned register pairs (holding the halves separately cost two MOVs per FFMA2 in the
+// first build of this file -- 31 % of all executed instructions were moves).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float lo_of(f32x2 v)
+{
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return a;
+}
+__device__ __forceinline__ float hi_of(f32x2 v)
+{
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return b;
+}
+__device__ __forceinline__ f32x2 ffma2p(f32x2 a, float k, f32x2 c)
+{
+    f32x2 d;
+    asm("{.reg .b64 kk;\n mov.b64 kk, {%2, %2};\n fma.rn.f32x2 %0, %1, kk, %3;}" : "=l"(d) : "l"(a), "f"(k), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 fmul2p(f32x2 a, float k)
+{
+    f32x2 d;
+    asm("{.reg .b64 kk;\n mov.b64 kk, {%2, %2};\n mul.rn.f32x2 %0, %1, kk;}" : "=l"(d) : "l"(a), "f"(k));
+    return d;
+}
+__device__ __forceinline__ f32x2 fadd2p(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
 __device__ __forceinline__ float fmax3(float a, float b, float c)
 {
     float d;
@@ -107,9 +148,9 @@ __device__ __forceinline__ void pipe_prefetch(float *stage, const float *__restr
 
 // The averaged window of one thread: v[j] = (row p, row p + HP) at column x0 - PAD + j.
 // mode: 0 = no flip, 1 = flip (+), 2 = flip with the partner negated (x-offset channels).
-template <int W, int H, int R, int NT, bool DIV255>
-__device__ __forceinline__ void pipe_window(const float *stage, bool has_fl, int p, int xs,
-                                            float2 (&v)[PipeGeom<W, H, R, NT>::NCOL])
+template <int W, int H, int R, int NT, bool FLIP, bool DIV255>
+__device__ __forceinline__ void pipe_window(const float *stage, int p, int xs,
+                                            f32x2 (&v)[PipeGeom<W, H, R, NT>::NCOL])
 {
     using G = PipeGeom<W, H, R, NT>;
     constexpr int PAD = G::PAD, SEG = G::SEG;
@@ -122,21 +163,21 @@ __device__ __forceinline__ void pipe_window(const float *stage, bool has_fl, int
         xc = xc < 0 ? 0 : (xc > W - 4 ? W - 4 : xc);  // out-of-map chunks are replaced below
         const float4 r0 = *reinterpret_cast<const float4 *>(a0 + xc);
         const float4 r1 = *reinterpret_cast<const float4 *>(a1 + xc);
-        float2 t0 = make_float2(r0.x, r1.x), t1 = make_float2(r0.y, r1.y);
-        float2 t2 = make_float2(r0.z, r1.z), t3 = make_float2(r0.w, r1.w);
-        if (has_fl) {
+        float e[8] = {r0.x, r1.x, r0.y, r1.y, r0.z, r1.z, r0.w, r1.w};
+        if (FLIP) {
             const float4 g0 = *reinterpret_cast<const float4 *>(f0 + (W - 4 - xc));
             const float4 g1 = *reinterpret_cast<const float4 *>(f1 + (W - 4 - xc));
-            t0.x = __fmul_rn(__fadd_rn(r0.x, g0.w), 0.5f); t0.y = __fmul_rn(__fadd_rn(r1.x, g1.w), 0.5f);
-            t1.x = __fmul_rn(__fadd_rn(r0.y, g0.z), 0.5f); t1.y = __fmul_rn(__fadd_rn(r1.y, g1.z), 0.5f);
-            t2.x = __fmul_rn(__fadd_rn(r0.z, g0.y), 0.5f); t2.y = __fmul_rn(__fadd_rn(r1.z, g1.y), 0.5f);
-            t3.x = __fmul_rn(__fadd_rn(r0.w, g0.x), 0.5f); t3.y = __fmul_rn(__fadd_rn(r1.w, g1.x), 0.5f);
+            e[0] = __fmul_rn(__fadd_rn(r0.x, g0.w), 0.5f); e[1] = __fmul_rn(__fadd_rn(r1.x, g1.w), 0.5f);
+            e[2] = __fmul_rn(__fadd_rn(r0.y, g0.z), 0.5f); e[3] = __fmul_rn(__fadd_rn(r1.y, g1.z), 0.5f);
+            e[4] = __fmul_rn(__fadd_rn(r0.z, g0.y), 0.5f); e[5] = __fmul_rn(__fadd_rn(r1.z, g1.y), 0.5f);
+            e[6] = __fmul_rn(__fadd_rn(r0.w, g0.x), 0.5f); e[7] = __fmul_rn(__fadd_rn(r1.w, g1.x), 0.5f);
         }
         if (DIV255) {
-            t0.x = div255(t0.x); t0.y = div255(t0.y); t1.x = div255(t1.x); t1.y = div255(t1.y);
-            t2.x = div255(t2.x); t2.y = div255(t2.y); t3.x = div255(t3.x); t3.y = div255(t3.y);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) e[i] = div255(e[i]);
         }
-        v[4 * q] = t0; v[4 * q + 1] = t1; v[4 * q + 2] = t2; v[4 * q + 3] = t3;
+        v[4 * q] = pk(e[0], e[1]); v[4 * q + 1] = pk(e[2], e[3]);
+        v[4 * q + 2] = pk(e[4], e[5]); v[4 * q + 3] = pk(e[6], e[7]);
     }
     // reflect-101 columns at the map borders: column -1-i <- column 1+i, column W+i <- column W-2-i
     if (xs == 0) {
@@ -151,7 +192,7 @@ __device__ __forceinline__ void pipe_window(const float *stage, bool has_fl, int
 
 // Row filter from the register window into T (stride ST, R halo rows above and below).
 template <int W, int H, int R, int NT>
-__device__ __forceinline__ void pipe_row_filter(const float2 (&v)[PipeGeom<W, H, R, NT>::NCOL],
+__device__ __forceinline__ void pipe_row_filter(const f32x2 (&v)[PipeGeom<W, H, R, NT>::NCOL],
                                                 float *T, int p, int xs)
 {
     using G = PipeGeom<W, H, R, NT>;
@@ -164,21 +205,21 @@ __device__ __forceinline__ void pipe_row_filter(const float2 (&v)[PipeGeom<W, H,
     float *h1 = T + (2 * (H - 1) - y1 + R) * G::ST + x0;
 #pragma unroll
     for (int o = 0; o < SEG; o += 2) {
-        float2 s0 = fmul2(v[PAD - R + o], Taps<R>::k(0)), s1 = fmul2(v[PAD - R + o + 1], Taps<R>::k(0));
+        f32x2 s0 = fmul2p(v[PAD - R + o], Taps<R>::k(0)), s1 = fmul2p(v[PAD - R + o + 1], Taps<R>::k(0));
 #pragma unroll
         for (int i = 1; i < 2 * R + 1; ++i) {
-            s0 = ffma2(v[PAD - R + o + i], Taps<R>::k(i), s0);
-            s1 = ffma2(v[PAD - R + o + 1 + i], Taps<R>::k(i), s1);
+            s0 = ffma2p(v[PAD - R + o + i], Taps<R>::k(i), s0);
+            s1 = ffma2p(v[PAD - R + o + 1 + i], Taps<R>::k(i), s1);
         }
-        const float2 ra = make_float2(s0.x, s1.x), rb = make_float2(s0.y, s1.y);
-        *reinterpret_cast<float2 *>(t0 + o) = ra;
-        *reinterpret_cast<float2 *>(t1 + o) = rb;
-        if (top) *reinterpret_cast<float2 *>(h0 + o) = ra;
-        if (bot) *reinterpret_cast<float2 *>(h1 + o) = rb;
+        const f32x2 ra = pk(lo_of(s0), lo_of(s1)), rb = pk(hi_of(s0), hi_of(s1));
+        *reinterpret_cast<f32x2 *>(t0 + o) = ra;
+        *reinterpret_cast<f32x2 *>(t1 + o) = rb;
+        if (top) *reinterpret_cast<f32x2 *>(h0 + o) = ra;
+        if (bot) *reinterpret_cast<f32x2 *>(h1 + o) = rb;
     }
 }
 
-// Column pass: thread = (column pair c, y segment); emit(y, x, float2) gets blurred (y,x),(y,x+1).
+// Column pass: thread = (column pair c, y segment); emit(y, x, a, b) gets the blurred values a = (y,x), b = (y,x+1).
 template <int W, int H, int R, int NT, typename Emit>
 __device__ __forceinline__ void pipe_col_pass(const float *T, Emit emit)
 {
@@ -186,15 +227,15 @@ __device__ __forceinline__ void pipe_col_pass(const float *T, Emit emit)
     constexpr int RS = G::RS;
     const int c = threadIdx.x % G::CP, ys = threadIdx.x / G::CP;
     const float *base = T + (ys * RS) * G::ST + 2 * c;
-    float2 t[RS + 2 * R];
+    f32x2 t[RS + 2 * R];
 #pragma unroll
-    for (int i = 0; i < RS + 2 * R; ++i) t[i] = *reinterpret_cast<const float2 *>(base + i * G::ST);
+    for (int i = 0; i < RS + 2 * R; ++i) t[i] = *reinterpret_cast<const f32x2 *>(base + i * G::ST);
 #pragma unroll
     for (int o = 0; o < RS; ++o) {
-        float2 s = ffma2(t[o + R], Taps<R>::k(R), make_float2(0.f, 0.f));
+        f32x2 s = ffma2p(t[o + R], Taps<R>::k(R), pk(0.f, 0.f));
 #pragma unroll
-        for (int i = 1; i <= R; ++i) s = ffma2(fadd2(t[o + R + i], t[o + R - i]), Taps<R>::k(R + i), s);
-        emit(ys * RS + o, 2 * c, s);
+        for (int i = 1; i <= R; ++i) s = ffma2p(fadd2p(t[o + R + i], t[o + R - i]), Taps<R>::k(R + i), s);
+        emit(ys * RS + o, 2 * c, lo_of(s), hi_of(s));
     }
 }
 
@@ -213,23 +254,23 @@ __device__ __forceinline__ float pipe_col_at(const float *T, int y, int x)
 // Raw first-index arg-max over the thread's own SEG columns of its two rows.
 // Step 1: local maxima (FMNMX only).  Step 2 (after the block max M is known): first index == M.
 template <int W, int H, int R, int NT>
-__device__ __forceinline__ float pipe_local_max(const float2 (&v)[PipeGeom<W, H, R, NT>::NCOL], float2 &fsum)
+__device__ __forceinline__ float pipe_local_max(const f32x2 (&v)[PipeGeom<W, H, R, NT>::NCOL], float &fsum)
 {
     using G = PipeGeom<W, H, R, NT>;
     float m0 = -INFINITY, m1 = -INFINITY;
-    float2 acc = make_float2(0.f, 0.f);
+    f32x2 acc = pk(0.f, 0.f);
 #pragma unroll
     for (int j = G::PAD; j < G::PAD + G::SEG; j += 2) {
-        m0 = fmax3(m0, v[j].x, v[j + 1].x);
-        m1 = fmax3(m1, v[j].y, v[j + 1].y);
-        acc = fadd2(acc, fadd2(v[j], v[j + 1]));
+        m0 = fmax3(m0, lo_of(v[j]), lo_of(v[j + 1]));
+        m1 = fmax3(m1, hi_of(v[j]), hi_of(v[j + 1]));
+        acc = fadd2p(acc, fadd2p(v[j], v[j + 1]));
     }
-    fsum = acc;
+    fsum = lo_of(acc) + hi_of(acc);
     return fmaxf(m0, m1);
 }
 
 template <int W, int H, int R, int NT>
-__device__ __forceinline__ int pipe_first_index(const float2 (&v)[PipeGeom<W, H, R, NT>::NCOL], float M,
+__device__ __forceinline__ int pipe_first_index(const f32x2 (&v)[PipeGeom<W, H, R, NT>::NCOL], float M,
                                                 int p, int xs)
 {
     using G = PipeGeom<W, H, R, NT>;
@@ -237,11 +278,11 @@ __device__ __forceinline__ int pipe_first_index(const float2 (&v)[PipeGeom<W, H,
     const int b0 = p * W + xs * G::SEG, b1 = b0 + G::HP * W;
 #pragma unroll
     for (int j = G::SEG - 1; j >= 0; --j) {  // descending, so the lowest index is written last
-        if (v[G::PAD + j].y == M) best = b1 + j;
+        if (hi_of(v[G::PAD + j]) == M) best = b1 + j;
     }
 #pragma unroll
     for (int j = G::SEG - 1; j >= 0; --j) {
-        if (v[G::PAD + j].x == M) best = b0 + j;
+        if (lo_of(v[G::PAD + j]) == M) best = b0 + j;
     }
     return best;
 }
