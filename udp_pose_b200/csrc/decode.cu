@@ -314,12 +314,14 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
     const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
     constexpr bool has_fl = FLIP;
 
+    PipePlan<W, H, R, NT> plan;
+    plan.init(smem);
+    MapWalk nxt;  // (person, joint) of the map being prefetched
+    nxt.init(blockIdx.x, (int)gridDim.x, p.K);
     auto src_of = [&](long long m) { return p.hm + m * (long long)hw; };
-    auto fl_of = [&](long long m) -> const float * {
+    auto fl_of = [&]() -> const float * {  // partner map of the map `nxt` points at
         if (!has_fl) return nullptr;
-        const long long n = m / p.K;
-        const int k = (int)(m - n * p.K);
-        return p.hm_flipped + (n * p.K + p.flip_perm[k]) * (long long)hw;
+        return p.hm_flipped + ((long long)nxt.n * p.K + __ldg(p.flip_perm + nxt.k)) * (long long)hw;
     };
     auto flush = [&](int count) {  // executed by one full warp
         if (lane < count) {
@@ -342,14 +344,15 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
 
     long long map = blockIdx.x;
     int s = 0, slot = 0;
-    if (map < maps) pipe_prefetch<W, H, R, NT>(smem, src_of(map), fl_of(map));
+    if (map < maps) pipe_prefetch<W, H, R, NT>(plan, 0, src_of(map), fl_of());
     cp_async_commit();
     for (; map < maps; map += gridDim.x, s ^= 1) {
         float *stage = smem + s * G::STAGE;
         cp_async_wait_all();
         __syncthreads();  // (A) this map has landed; the previous map's T is dead
         const long long next = map + gridDim.x;
-        if (next < maps) pipe_prefetch<W, H, R, NT>(smem + (s ^ 1) * G::STAGE, src_of(next), fl_of(next));
+        nxt.advance();
+        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
         cp_async_commit();
         if (threadIdx.x == 0) s_idx = 0x7fffffff;
         // mailbox full: one warp finishes the 32 queued maps.  No extra barrier: the next mailbox
@@ -372,7 +375,7 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
             cp_async_wait_all();
             __syncthreads();
             decode_gauss_generic_map<POST>(p, smem, map);
-            if (next < maps) pipe_prefetch<W, H, R, NT>(smem + (s ^ 1) * G::STAGE, src_of(next), fl_of(next));
+            if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
             cp_async_commit();
             continue;
         }

@@ -15,7 +15,7 @@
 // the two windows (and their flipped counterparts) straight from global memory after the
 // argmax is known, and runs the same row-then-column FMA order on them: identical bits,
 // two thirds of the input tensor never leave HBM.
-#include "blur_fast.cuh"
+#include "decode_pipe.cuh"
 
 namespace udp {
 
@@ -94,7 +94,7 @@ __device__ __forceinline__ void offset_finish(const DecodeOffsetArgs &p, long lo
 }
 
 // Generic path: any (w, h) with w % 4 == 0, NaN-exact argmax.
-__device__ __forceinline__ void decode_offset_generic(const DecodeOffsetArgs &p, float *smem,
+__device__ __noinline__ void decode_offset_generic(const DecodeOffsetArgs &p, float *smem,
                                                       long long map, int n, const float *src,
                                                       const float *fl)
 {
@@ -137,49 +137,202 @@ __global__ void decode_offset_kernel(DecodeOffsetArgs p)
     decode_offset_generic(p, smem, map, n, src, fl);
 }
 
-// Fast path: compile-time map shape, packed-FP32 blur (blur_fast.cuh).  Maps holding a
+// The vote (:160-174) of the streaming kernel's batched tail, split in two so that every thread
+// of the CTA shares the scattered loads:
+//   offset_row_item  one (map, channel, window row): gather 7 (+7 flipped) offsets straight from
+//                    global memory, average, scale by KPD, cv2's left-to-right row FMA chain;
+//   offset_final     one map: symmetric column combine of the 2 x 7 row results, add to the
+//                    integer peak, inverse affine, stores.
+__device__ __forceinline__ float offset_row_item(const DecodeOffsetArgs &p, long long map, float bv, int bi,
+                                                 int ch, int i)
+{
+    const int w = p.w, h = p.h, hw = h * w;
+    const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
+    const bool mask = bv > 0.0f;
+    const int ix = mask ? bi % w : 0, iy = mask ? bi / w : 0;
+    const int yo = reflect101(iy - 3 + i, h) * w;
+    const float *a = p.out + (map * 3 + 1 + ch) * (long long)hw + yo;
+    const float *f = p.out_flipped
+                         ? p.out_flipped + (((long long)n * p.K + p.flip_perm[k]) * 3 + 1 + ch) * (long long)hw + yo
+                         : nullptr;
+    const float fs = ch == 0 ? -1.0f : 1.0f;  // x offsets change sign under the mirror (:40)
+    float v[7];
+#pragma unroll
+    for (int t = 0; t < 7; ++t) {
+        const int xx = reflect101(ix - 3 + t, w);
+        v[t] = __ldg(a + xx);
+        if (f) v[t] = __fmul_rn(__fadd_rn(v[t], fs * __ldg(f + (w - 1 - xx))), 0.5f);
+        v[t] = __fmul_rn(v[t], p.kpd);  // :161-162
+    }
+    float sacc = __fmul_rn(v[0], Taps<3>::k(0));
+#pragma unroll
+    for (int t = 1; t < 7; ++t) sacc = fmaf(v[t], Taps<3>::k(t), sacc);
+    return sacc;
+}
+
+__device__ __forceinline__ void offset_final(const DecodeOffsetArgs &p, long long map, float bv, int bi,
+                                             const float *rows /* [2][7] */)
+{
+    const int w = p.w, h = p.h;
+    const int n = (int)(map / p.K);
+    const bool mask = bv > 0.0f;
+    const int ix = mask ? bi % w : 0, iy = mask ? bi / w : 0;
+    float offs[2];
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+        const float *t = rows + ch * 7;
+        float sacc = fmaf(t[3], Taps<3>::k(3), 0.0f);
+        sacc = fmaf(__fadd_rn(t[4], t[2]), Taps<3>::k(4), sacc);
+        sacc = fmaf(__fadd_rn(t[5], t[1]), Taps<3>::k(5), sacc);
+        sacc = fmaf(__fadd_rn(t[6], t[0]), Taps<3>::k(6), sacc);
+        offs[ch] = sacc;
+    }
+    const float px = __fadd_rn((float)ix, offs[0]);  // :173-174
+    const float py = __fadd_rn((float)iy, offs[1]);
+    double ox = px, oy = py;
+    if (p.center) {
+        const CS cs = load_cs(p.center, p.scale, p.cs_f64, n);
+        transform_pred((double)px, (double)py, cs, p.cs_f64, false, w, h, ox, oy);
+    }
+    p.preds[map * 2] = (float)ox;
+    p.preds[map * 2 + 1] = (float)oy;
+    if (p.preds_in) {
+        p.preds_in[map * 2] = __fmul_rn(__fdiv_rn(px, (float)(w - 1.0)), (float)(4 * w - 1.0));
+        p.preds_in[map * 2 + 1] = __fmul_rn(__fdiv_rn(py, (float)(h - 1.0)), (float)(4 * h - 1.0));
+    }
+    p.maxvals[map] = bv;
+    if (p.argmax_idx) p.argmax_idx[map] = bi;
+    if (p.packed) { float *q = p.packed + map * 3; q[0] = (float)ox; q[1] = (float)oy; q[2] = bv; }
+}
+
+// Streaming fast path (decode_pipe.cuh): persistent CTAs, 2-stage cp.async pipeline over the
+// classification maps, 15x15 packed-FP32 blur, arg-max on the blurred map.  Three barriers per
+// map; the per-warp arg-max candidates go to a 32-entry mailbox.  Every 32 maps all threads
+// share the 32 x 14 offset-window rows (scattered global loads, all in flight together), and
+// after the next barrier one warp finishes the 32 maps, one per lane.  Maps holding a
 // non-finite value are re-done by the generic path above (np.argmax's NaN rule).
-template <int W, int H, int NT>
-__global__ void __launch_bounds__(NT) decode_offset_fast_kernel(DecodeOffsetArgs p)
+template <int W, int H, int NT, bool FLIP>
+__global__ void __launch_bounds__(NT) decode_offset_pipe_kernel(DecodeOffsetArgs p, long long maps)
 {
     constexpr int R = 7;
-    using G = FastGeom<W, H, R, NT>;
+    using G = PipeGeom<W, H, R, NT>;
+    constexpr int NW = G::NWARP, NBOX = 32;
+    constexpr int B_V = 0, B_I = NW, B_MAP = 2 * NW, BOXW = 2 * NW + 1;
     extern __shared__ __align__(16) float smem[];
-    __shared__ float red_v[32];
-    __shared__ int red_i[32];
+    __shared__ float s_box[NBOX * BOXW];
+    __shared__ float s_rows[NBOX * 14];
     constexpr int hw = H * W;
-    const long long map = blockIdx.x;
-    const int n = (int)(map / p.K), k = (int)(map - (long long)n * p.K);
-    const float *src = p.out + (map * 3) * (long long)hw;
-    const int kp = p.out_flipped ? p.flip_perm[k] : k;
-    const float *fl = p.out_flipped ? p.out_flipped + (((long long)n * p.K + kp) * 3) * (long long)hw : nullptr;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
 
-    float2 *A2 = reinterpret_cast<float2 *>(smem);
-    float *T = smem + G::A2_BYTES / 4;
-    float rv, fsum;
-    int ri;
-    fast_load<W, H, R, NT>(src, fl, 0.0f, A2, rv, ri, fsum);
-    if (__syncthreads_or(!(fabsf(fsum) < INFINITY))) {  // NaN / inf somewhere in the map
-        decode_offset_generic(p, smem, map, n, src, fl);
-        return;
+    PipePlan<W, H, R, NT> plan;
+    plan.init(smem);
+    MapWalk nxt;  // (person, joint) of the map being prefetched
+    nxt.init(blockIdx.x, (int)gridDim.x, p.K);
+    auto src_of = [&](long long m) { return p.out + (m * 3) * (long long)hw; };
+    auto fl_of = [&]() -> const float * {  // partner map of the map `nxt` points at
+        if (!FLIP) return nullptr;
+        return p.out_flipped + (((long long)nxt.n * p.K + __ldg(p.flip_perm + nxt.k)) * 3) * (long long)hw;
+    };
+    auto entry = [&](int e, float &bv, int &bi) -> long long {  // combine the per-warp candidates
+        const float *b = s_box + e * BOXW;
+        bv = b[B_V];
+        bi = __float_as_int(b[B_I]);
+#pragma unroll
+        for (int q = 1; q < NW; ++q) {
+            const float v = b[B_V + q];
+            const int i = __float_as_int(b[B_I + q]);
+            if (arg_better(v, i, bv, bi)) { bv = v; bi = i; }
+        }
+        return (long long)__float_as_int(b[B_MAP]);
+    };
+    auto flush_rows = [&](int count) {  // all threads: (map, channel, row) items
+        for (int item = threadIdx.x; item < count * 14; item += NT) {
+            const int e = item / 14, r = item - e * 14;
+            float bv;
+            int bi;
+            const long long m = entry(e, bv, bi);
+            s_rows[item] = offset_row_item(p, m, bv, bi, r / 7, r - (r / 7) * 7);
+        }
+    };
+    auto flush_final = [&](int count) {  // one full warp, one map per lane
+        if (lane < count) {
+            float bv;
+            int bi;
+            const long long m = entry(lane, bv, bi);
+            offset_final(p, m, bv, bi, s_rows + lane * 14);
+        }
+    };
+
+    long long map = blockIdx.x;
+    int s = 0, slot = 0;
+    if (map < maps) pipe_prefetch<W, H, R, NT>(plan, 0, src_of(map), fl_of());
+    cp_async_commit();
+    for (; map < maps; map += gridDim.x, s ^= 1) {
+        float *stage = smem + s * G::STAGE;
+        cp_async_wait_all();
+        __syncthreads();  // (A) this map has landed; the previous map's T is dead
+        const long long next = map + gridDim.x;
+        nxt.advance();
+        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
+        cp_async_commit();
+        // mailbox full: everyone gathers offset rows now; warp 0 finishes the maps after barrier (B).
+        // No extra barrier: the next mailbox / s_rows write comes after (C), resp. the next flush.
+        const bool finish = slot == NBOX;
+        if (finish) { flush_rows(NBOX); slot = 0; }
+
+        f32x2 v[G::NCOL];
+        pipe_window<W, H, R, NT, FLIP, false>(stage, pr, xs, v);
+        f32x2 acc = pk(0.f, 0.f);
+#pragma unroll
+        for (int j = G::PAD; j < G::PAD + G::SEG; j += 2) acc = fadd2p(acc, fadd2p(v[j], v[j + 1]));
+        const bool bad = !(fabsf(lo_of(acc) + hi_of(acc)) < INFINITY);
+        const bool anybad = __syncthreads_or(bad);
+        if (finish && warp == 0) flush_final(NBOX);
+        if (anybad) {  // NaN / inf somewhere in the map
+            cp_async_wait_all();
+            __syncthreads();
+            const int gn = (int)(map / p.K), gk = (int)(map - (long long)gn * p.K);
+            const float *gfl = FLIP ? p.out_flipped + (((long long)gn * p.K + p.flip_perm[gk]) * 3) * (long long)hw
+                                    : nullptr;
+            decode_offset_generic(p, smem, map, gn, src_of(map), gfl);
+            __syncthreads();
+            if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
+            cp_async_commit();
+            continue;
+        }
+        // (B) the raw stage is consumed: T may overwrite it
+        float *T = stage;
+        pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
+        __syncthreads();  // (C) T complete
+        float v0 = -INFINITY, v1 = -INFINITY;
+        int y0 = 0, y1 = 0;
+        pipe_col_pass<W, H, R, NT>(T, [&](int y, int, float a, float b) {
+            if (a > v0) { v0 = a; y0 = y; }
+            if (b > v1) { v1 = b; y1 = y; }
+        });
+        const int xc = 2 * (threadIdx.x % G::CP);
+        float bv = v0;
+        int bi = y0 * W + xc;
+        if (arg_better(v1, y1 * W + xc + 1, bv, bi)) { bv = v1; bi = y1 * W + xc + 1; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        float *box = s_box + slot * BOXW;
+        if (lane == 0) { box[B_V + warp] = bv; box[B_I + warp] = __int_as_float(bi); }
+        if (threadIdx.x == 0) box[B_MAP] = __int_as_float((int)map);
+        ++slot;
     }
-    fast_pads<W, H, R, NT>(A2);
+    cp_async_wait_all();
     __syncthreads();
-    fast_row_pass<W, H, R, NT>(A2, T);
-    __syncthreads();
-    float v0 = -INFINITY, v1 = -INFINITY;
-    int y0 = 0, y1 = 0, xc = 0;
-    fast_col_pass<W, H, R, NT>(T, [&](int y, int x, float2 s) {
-        xc = x;
-        if (s.x > v0) { v0 = s.x; y0 = y; }
-        if (s.y > v1) { v1 = s.y; y1 = y; }
-    });
-    float bv = v0;
-    int bi = y0 * W + xc;
-    if (arg_better(v1, y1 * W + xc + 1, bv, bi)) { bv = v1; bi = y1 * W + xc + 1; }
-    if (threadIdx.x >= G::CP * G::YS) { bv = -INFINITY; bi = 0x7fffffff; }
-    block_argmax(bv, bi, red_v, red_i);
-    offset_finish(p, map, n, src, fl, bv, bi);
+    if (slot) {
+        flush_rows(slot);
+        __syncthreads();
+        if (warp == 0) flush_final(slot);
+    }
 }
 
 }  // namespace udp
@@ -201,21 +354,26 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
     size_t gsmem = udp::BlurGeom<7>::smem_floats(w, h) * sizeof(float);
     if (gsmem > 200 * 1024) return UDP_EINVAL;
     if (!udp_force_generic()) {
-#define UDP_OFF_FAST(WW, HH, NT)                                                                 \
+#define UDP_OFF_PIPE(WW, HH, NT)                                                                 \
         if (w == WW && h == HH) {                                                                \
-            using G = udp::FastGeom<WW, HH, 7, NT>;                                                \
-            size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                                       \
-            auto kern = udp::decode_offset_fast_kernel<WW, HH, NT>;                                \
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-            if (e != cudaSuccess) return (int)e;                                                   \
-            kern<<<(unsigned)maps, NT, smem, (cudaStream_t)stream>>>(a);                           \
-            UDP_LAUNCH_CHECK();                                                                    \
-            return 0;                                                                              \
+            using G = udp::PipeGeom<WW, HH, 7, NT>;                                              \
+            const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
+            void (*kern)(udp::DecodeOffsetArgs, long long) =                                     \
+                out_flipped ? udp::decode_offset_pipe_kernel<WW, HH, NT, true>                   \
+                            : udp::decode_offset_pipe_kernel<WW, HH, NT, false>;                 \
+            int per_sm = 0;                                                                      \
+            int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
+            if (rc) return rc;                                                                   \
+            long long grid = (long long)per_sm * udp::sm_count();                                \
+            if (grid > maps) grid = maps;                                                        \
+            kern<<<(unsigned)grid, NT, smem, (cudaStream_t)stream>>>(a, maps);                   \
+            UDP_LAUNCH_CHECK();                                                                  \
+            return 0;                                                                            \
         }
-        UDP_OFF_FAST(48, 64, 64)
-        UDP_OFF_FAST(64, 64, 64)
-        UDP_OFF_FAST(72, 96, 128)
-#undef UDP_OFF_FAST
+        UDP_OFF_PIPE(48, 64, 96)
+        UDP_OFF_PIPE(64, 64, 128)
+        UDP_OFF_PIPE(72, 96, 288)
+#undef UDP_OFF_PIPE
     }
     cudaError_t e = cudaFuncSetAttribute(udp::decode_offset_kernel,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsmem);

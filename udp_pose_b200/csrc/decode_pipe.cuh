@@ -129,22 +129,64 @@ struct PipeGeom {
 };
 
 // Asynchronous copy of one map (and its flip partner) into a stage, rows at stride SR.
+// A thread copies the same 16-byte column chunk of every (NT / (W/4))-th row, so source and
+// destination offsets are a per-thread constant plus compile-time immediates (the first build
+// recomputed row/column by division for each of the 32 copies: ~100 integer instructions
+// per thread and map).
 template <int W, int H, int R, int NT>
-__device__ __forceinline__ void pipe_prefetch(float *stage, const float *__restrict__ src,
-                                              const float *__restrict__ fl)
+struct PipePlan {
+    using G = PipeGeom<W, H, R, NT>;
+    static constexpr int W4 = W / 4;
+    static_assert(NT % W4 == 0, "NT must be a multiple of W/4");
+    static constexpr int RPI = NT / W4;  // rows per iteration
+    static_assert(H % RPI == 0, "H must be a multiple of NT/(W/4)");
+    static constexpr int ITER = H / RPI;
+    unsigned dst;  // shared-space byte address inside stage 0
+    unsigned src;  // float offset inside the map
+    __device__ __forceinline__ void init(const float *smem_base)
+    {
+        const int ty = threadIdx.x / W4, tx = threadIdx.x - ty * W4;
+        dst = (unsigned)__cvta_generic_to_shared(smem_base) + (unsigned)(ty * G::SR + tx * 4) * 4u;
+        src = threadIdx.x * 4;
+    }
+};
+
+template <int W, int H, int R, int NT>
+__device__ __forceinline__ void pipe_prefetch(const PipePlan<W, H, R, NT> &pl, int stage,
+                                              const float *__restrict__ src, const float *__restrict__ fl)
 {
     using G = PipeGeom<W, H, R, NT>;
-    constexpr int W4 = W / 4, ITEMS = H * W4;
+    using P = PipePlan<W, H, R, NT>;
+    const unsigned d0 = pl.dst + (unsigned)stage * (unsigned)(G::STAGE * 4);
+    const float *s0 = src + pl.src;
 #pragma unroll
-    for (int it0 = 0; it0 < ITEMS; it0 += NT) {
-        const int it = it0 + threadIdx.x;
-        if (ITEMS % NT == 0 || it < ITEMS) {
-            const int y = it / W4, x = (it - y * W4) << 2;
-            cp_async16(stage + y * G::SR + x, src + it * 4);
-            if (fl) cp_async16(stage + G::RAW + y * G::SR + x, fl + it * 4);
-        }
+    for (int j = 0; j < P::ITER; ++j)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + (unsigned)(j * P::RPI * G::SR * 4)),
+                     "l"(s0 + j * NT * 4) : "memory");
+    if (fl) {
+        const float *f0 = fl + pl.src;
+#pragma unroll
+        for (int j = 0; j < P::ITER; ++j)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + (unsigned)((G::RAW + j * P::RPI * G::SR) * 4)),
+                         "l"(f0 + j * NT * 4) : "memory");
     }
 }
+
+// (person, joint) of a map index that advances by a fixed step, without 64-bit divisions.
+struct MapWalk {
+    int n, k, sn, sk, K;
+    __device__ __forceinline__ void init(long long map, int step, int K_)
+    {
+        K = K_;
+        n = (int)(map / K_); k = (int)(map - (long long)n * K_);
+        sn = step / K_; sk = step - sn * K_;
+    }
+    __device__ __forceinline__ void advance()
+    {
+        n += sn; k += sk;
+        if (k >= K) { k -= K; ++n; }
+    }
+};
 
 // The averaged window of one thread: v[j] = (row p, row p + HP) at column x0 - PAD + j.
 // mode: 0 = no flip, 1 = flip (+), 2 = flip with the partner negated (x-offset channels).
