@@ -14,7 +14,7 @@
 // rint(M00*x*1024), rint(M10*x*1024) and the per-row bases are float64 and are computed
 // once per CTA into shared memory; the per-pixel work is integer only.  The finished
 // ROWS x W x 3 byte tile is staged in shared memory and leaves as 16-byte streaming stores.
-#include "common.cuh"
+#include "decode_pipe.cuh"
 
 namespace udp {
 
@@ -136,6 +136,236 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
     }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Second-generation crop: 32 x 32 output tiles gathered from a shared-memory copy of the
+// tile's source footprint.
+//
+// ncu on the kernel above (profiles/r01_crop_v6_ncu.txt): the L1 data pipe is the limiter --
+// 81 % of peak wavefronts, 4.3 wavefronts per global load request, because 60 % of the
+// training-time boxes are rotated and a warp's 32 consecutive output pixels then walk
+// diagonally through up to 32 source rows (one 128-byte line each, six loads per pixel), and
+// every border pixel diverges into the out-of-line path.  Here:
+//   * the footprint (axis-aligned bounding box of the tile's taps, exact because the Q10
+//     column deltas and row bases are monotonic) is copied with 16-byte cp.async chunks that
+//     keep the global 16-byte phase, so any image alignment / stride works; rows and chunks
+//     outside the image buffer are zero-filled, and for tiles that cross the left/right image
+//     edge a fix-up pass zeroes the out-of-image columns: the gather itself is branch-free and
+//     OpenCV's constant-0 border falls out of the data;
+//   * the gather reads shared memory, where only bank conflicts matter, not 128-byte lines;
+//   * the bilinear weights go through two IDP.2A per channel (16-bit weight pairs wy*wx
+//     against byte pairs) instead of dp4a + two IMADs;
+//   * a warp's 32 pixels (96 bytes) are repacked with two shuffles and leave as 24 aligned
+//     4-byte stores -- no output tile in shared memory, no second barrier.
+// Arithmetic is the same integer formula as above: bit-exact with cv2.warpAffine.
+// ---------------------------------------------------------------------------------------
+constexpr int CT = 32;                       // tile edge (output pixels)
+constexpr int CT_THREADS = 128;              // 4 warps, 8 tile rows each
+constexpr int CT_SMEM = 24 * 1024;           // footprint buffer (bytes), + 16 bytes slack
+
+__device__ __forceinline__ void zero_bytes(uint8_t *base, int lo, int hi)
+{
+    while (lo < hi && (lo & 3)) base[lo++] = 0;
+    while (lo + 4 <= hi) { *reinterpret_cast<uint32_t *>(base + lo) = 0u; lo += 4; }
+    while (lo < hi) base[lo++] = 0;
+}
+
+struct TileGeom {
+    int xa, ya, ncols, nrows, maxc;
+};
+
+__device__ __forceinline__ uint32_t lds_u32(unsigned addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+// One output pixel from the footprint copy.  K0 folds the buffer's shared-space address,
+// shift0 - ya*pitch - 3*xa, so a tap address is sy*pitch + 3*sx + K0.
+template <bool UNIFORM_PHASE>
+__device__ __forceinline__ uint32_t crop_tile_pixel(int X, int Y, int pitch, int K0, int shift0, int ya, int ssm)
+{
+    const int sx = X >> 10, sy = Y >> 10;
+    const uint32_t fx = ((uint32_t)X >> 5) & 31u, fy = ((uint32_t)Y >> 5) & 31u;
+    int a0, a1;
+    if (UNIFORM_PHASE) {  // stride % 16 == 0: every row has the phase shift0
+        a0 = sy * pitch + (3 * sx + K0);
+        a1 = a0 + pitch;
+    } else {
+        const int ry = sy - ya;
+        const int s0 = (shift0 + ry * ssm) & 15, s1 = (s0 + ssm) & 15;
+        a0 = sy * pitch + (3 * sx + K0) + (s0 - shift0);
+        a1 = a0 + pitch + (s1 - s0);
+    }
+    // the buffer is 16-byte aligned in shared space, so (a & 3) is the byte phase of the tap
+    const unsigned q0 = (unsigned)a0 & ~3u, q1 = (unsigned)a1 & ~3u;
+    const uint32_t u0 = lds_u32(q0), u1 = lds_u32(q0 + 4), u2 = lds_u32(q0 + 8);
+    const uint32_t v0 = lds_u32(q1), v1 = lds_u32(q1 + 4), v2 = lds_u32(q1 + 8);
+    const uint32_t h0 = (uint32_t)a0 << 3, h1 = (uint32_t)a1 << 3;  // funnel shift uses bits 0..4
+    const uint32_t lo0 = __funnelshift_r(u0, u1, h0), hi0 = __funnelshift_r(u1, u2, h0);
+    const uint32_t lo1 = __funnelshift_r(v0, v1, h1), hi1 = __funnelshift_r(v1, v2, h1);
+    const uint32_t c_r = __byte_perm(lo0, lo1, 0x7430);  // [r00 r01 r10 r11]
+    const uint32_t c_t = __byte_perm(lo0, hi0, 0x5241);  // [g00 g01 b00 b01]
+    const uint32_t c_b = __byte_perm(lo1, hi1, 0x5241);  // [g10 g11 b10 b11]
+    const uint32_t wxp = fx * 0xffffu + 32u;             // (32 - fx) | fx << 16
+    const uint32_t W0 = (32u - fy) * wxp, W1 = fy * wxp; // (wy*wx0 | wy*wx1 << 16), each <= 1024
+    const uint32_t Sr = __dp2a_hi(W1, c_r, __dp2a_lo(W0, c_r, 512u));
+    const uint32_t Sg = __dp2a_lo(W1, c_b, __dp2a_lo(W0, c_t, 512u));
+    const uint32_t Sb = __dp2a_hi(W1, c_b, __dp2a_hi(W0, c_t, 512u));
+    // (S + 512) >> 10 is byte 2 of S << 6
+    return __byte_perm(__byte_perm(Sr << 6, Sg << 6, 0x4462), Sb << 6, 0x4610);
+}
+
+__device__ __forceinline__ int q10_col(double m, int x) { return __double2int_rn(__dmul_rn(__dmul_rn(m, (double)x), 1024.0)); }
+__device__ __forceinline__ int q10_row(double m, double c, int y)
+{
+    return __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m, (double)y), c), 1024.0)) + 16;
+}
+
+__global__ void __launch_bounds__(CT_THREADS)
+warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
+                           const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H,
+                           int tiles_x)
+{
+    extern __shared__ __align__(16) unsigned char fp[];  // footprint copy
+    const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
+
+    const int n = blockIdx.y, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int ty = blockIdx.x / tiles_x, tx = blockIdx.x - ty * tiles_x;
+    const int x0 = tx * CT, y0 = ty * CT;
+    const float *m = M + 6 * (size_t)n;
+    const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
+    // Q10 column deltas of this lane's column; Q10 row bases of one row per lane:
+    // lanes 0..7 hold this warp's rows (warp + 4*lane), lane 8 / lanes >= 9 the tile's first / last row
+    const int adx = q10_col(m00, x0 + lane), bdx = q10_col(m10, x0 + lane);
+    const int myrow = lane < 8 ? warp + 4 * lane : (lane == 8 ? 0 : CT - 1);
+    const int rX = q10_row(m01, m02, y0 + myrow), rY = q10_row(m11, m12, y0 + myrow);
+
+    const uint8_t *src = src_ptrs[n];
+    const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
+    const int ssm = ss & 15;
+    const int A0 = __shfl_sync(0xffffffffu, adx, 0), A1 = __shfl_sync(0xffffffffu, adx, CT - 1);
+    const int B0 = __shfl_sync(0xffffffffu, bdx, 0), B1 = __shfl_sync(0xffffffffu, bdx, CT - 1);
+    const int Amin = min(A0, A1), Amax = max(A0, A1), Bmin = min(B0, B1), Bmax = max(B0, B1);
+    // per-lane constants of the 96-byte row repack: word `lane` holds bytes 4*lane .. 4*lane+3
+    int p0 = min((4 * lane) / 3, 30);
+    uint32_t osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
+    asm volatile("" : "+r"(p0), "+r"(osel));  // keep them in registers (ptxas rematerialised them per pixel)
+    uint8_t *const out0 = dst + (((size_t)n * H + y0 + warp) * W + x0) * 3 + 4 * lane;
+    const size_t out_step = (size_t)(CT_THREADS / 32) * W * 3;
+
+    auto bbox = [&](int Xa, int Xb, int Ya, int Yb) {  // footprint of tile rows whose first/last bases are given
+        TileGeom g;
+        g.xa = (min(Xa, Xb) + Amin) >> 10;
+        g.ya = (min(Ya, Yb) + Bmin) >> 10;
+        g.ncols = ((max(Xa, Xb) + Amax) >> 10) + 2 - g.xa;
+        g.nrows = ((max(Ya, Yb) + Bmax) >> 10) + 2 - g.ya;
+        g.maxc = ((30 + 3 * g.ncols) >> 4) | 1;  // 16-byte chunks per row at worst-case phase; odd count
+        return g;
+    };
+    auto bbox_rows = [&](int ry0, int rows) {  // (multi-pass only) recompute the two row bases
+        return bbox(q10_row(m01, m02, y0 + ry0), q10_row(m01, m02, y0 + ry0 + rows - 1),
+                    q10_row(m11, m12, y0 + ry0), q10_row(m11, m12, y0 + ry0 + rows - 1));
+    };
+    TileGeom g = bbox(__shfl_sync(0xffffffffu, rX, 8), __shfl_sync(0xffffffffu, rX, 9),
+                      __shfl_sync(0xffffffffu, rY, 8), __shfl_sync(0xffffffffu, rY, 9));
+    // rows per pass: the whole tile unless its footprint does not fit the buffer (large scale)
+    int nr = CT;
+    if (g.nrows * (g.maxc << 4) > CT_SMEM) {
+        for (nr = CT / 2; nr > 1; nr >>= 1) {
+            bool fits = true;
+            for (int ry0 = 0; ry0 < CT; ry0 += nr) {
+                const TileGeom h = bbox_rows(ry0, nr);
+                if ((long long)h.nrows * (h.maxc << 4) > CT_SMEM) { fits = false; break; }
+            }
+            if (fits) break;
+        }
+    }
+
+    for (int ry0 = 0; ry0 < CT; ry0 += nr) {
+        if (nr != CT) g = bbox_rows(ry0, nr);
+        const int pitch = g.maxc << 4;
+        const bool direct = (long long)g.nrows * pitch > CT_SMEM;  // absurd scale: per-pixel global path
+        // 16-byte phase of pixel (xa, ya); row r of the footprint has phase (shift0 + r*ssm) & 15
+        const int shift0 = (int)(((long long)(uintptr_t)src + (long long)g.ya * ss + 3LL * g.xa) & 15);
+        if (!direct) {
+            // ---- stage the footprint: 16-byte cp.async chunks, flat index = (row, chunk) = smem offset / 16.
+            // Chunk addresses are 32-bit byte offsets from the 16-byte-aligned start of the image buffer
+            // (images are < 2 GiB); a chunk is copied iff it lies inside the buffer, else zero-filled.
+            const int total = g.nrows * g.maxc;
+            const float rinv = __frcp_rn((float)g.maxc);
+            const int dr = (int)(((float)CT_THREADS + 0.5f) * rinv), dc = CT_THREADS - dr * g.maxc;
+            int r = (int)(((float)t + 0.5f) * rinv), c = t - r * g.maxc;  // exact: t, CT_THREADS << 2^20
+            const char *buf = reinterpret_cast<const char *>((uintptr_t)src & ~(uintptr_t)15);
+            const int lead = (int)((uintptr_t)src & 15);
+            const unsigned lim = sh > 0 && sw > 0 ? (unsigned)((((long long)(sh - 1) * ss + 3LL * sw + lead + 15) & ~15LL) - 16) : 0u;
+            const int base_off = lead + 3 * g.xa;  // offset of pixel (xa, row 0) from buf
+            unsigned d = fpa + ((unsigned)t << 4);
+            const long long off_lo = (long long)g.ya * ss + base_off - 15;
+            const long long off_hi = (long long)(g.ya + g.nrows - 1) * ss + base_off + pitch - 16;
+            if (g.ya >= 0 && g.ya + g.nrows <= sh && off_lo >= 0 && off_hi <= (long long)lim) {  // every chunk is in the buffer
+                for (int idx = t; idx < total; idx += CT_THREADS, d += CT_THREADS * 16) {
+                    const int off = (g.ya + r) * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
+                    r += dr; c += dc;
+                    if (c >= g.maxc) { c -= g.maxc; ++r; }
+                }
+            } else {
+                for (int idx = t; idx < total; idx += CT_THREADS, d += CT_THREADS * 16) {
+                    const int y = g.ya + r;
+                    const int off = y * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
+                    if ((unsigned)y < (unsigned)sh && (unsigned)off <= lim && sw > 0)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
+                    else
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(d), "r"(0) : "memory");
+                    r += dr; c += dc;
+                    if (c >= g.maxc) { c -= g.maxc; ++r; }
+                }
+            }
+            cp_async_commit();
+            cp_async_wait_all();
+            __syncthreads();
+            if (g.xa < 0 || g.xa + g.ncols > sw) {  // zero the columns left / right of the image
+                for (int rr = t; rr < g.nrows; rr += CT_THREADS) {
+                    const int y = g.ya + rr;
+                    if (y < 0 || y >= sh) continue;
+                    const int shr = (shift0 + rr * ssm) & 15;
+                    uint8_t *base = fp + rr * pitch;
+                    if (g.xa < 0) zero_bytes(base, shr, shr + 3 * min(g.ncols, -g.xa));
+                    if (g.xa + g.ncols > sw) zero_bytes(base, shr + 3 * max(0, sw - g.xa), shr + 3 * g.ncols);
+                }
+                __syncthreads();
+            }
+        }
+        const int K0 = (int)fpa + shift0 - g.ya * pitch - 3 * g.xa;
+        uint8_t *outp = out0 + (size_t)ry0 * W * 3;
+        // rows of this pass owned by this warp: ry0 + warp + 4*i.  Their bases sit in lane
+        // (row - warp) / 4 when nr == CT; in multi-pass mode they are recomputed.
+#define UDP_CROP_ROWS(PIXEL_EXPR)                                                                   \
+        for (int r = ry0 + warp; r < ry0 + nr; r += CT_THREADS / 32, outp += out_step) {          \
+            int X, Y;                                                                              \
+            if (nr == CT) { X = __shfl_sync(0xffffffffu, rX, r >> 2); Y = __shfl_sync(0xffffffffu, rY, r >> 2); } \
+            else { X = q10_row(m01, m02, y0 + r); Y = q10_row(m11, m12, y0 + r); }                 \
+            X += adx; Y += bdx;                                                                    \
+            const uint32_t px = (PIXEL_EXPR);                                                      \
+            const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1); \
+            if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);        \
+        }
+        if (direct) {
+            UDP_CROP_ROWS(crop_border_pixel(src, sh, sw, ss, X, Y))
+        } else if (ssm == 0) {
+#pragma unroll 2
+            UDP_CROP_ROWS(crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
+        } else {
+#pragma unroll 2
+            UDP_CROP_ROWS(crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
+        }
+#undef UDP_CROP_ROWS
+        if (ry0 + nr < CT) __syncthreads();  // the next pass overwrites the footprint buffer
+    }
+}
+
 }  // namespace udp
 
 extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h,
@@ -145,6 +375,17 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
     if (N < 0 || W < 1 || H < 1 || (W & 1)) return UDP_EINVAL;
     if (N == 0) return 0;
     if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst) return UDP_EINVAL;
+    if (!udp_force_generic() && W % udp::CT == 0 && H % udp::CT == 0 && ((uintptr_t)dst & 3) == 0) {
+        const int tiles_x = W / udp::CT, tiles = tiles_x * (H / udp::CT);
+        for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
+            const int nn = N - n0 < 65535 ? N - n0 : 65535;
+            udp::warp_affine_u8_tile_kernel<<<dim3(tiles, nn), udp::CT_THREADS, udp::CT_SMEM + 16, (cudaStream_t)stream>>>(
+                src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
+                dst + (size_t)n0 * H * W * 3, W, H, tiles_x);
+            UDP_LAUNCH_CHECK();
+        }
+        return 0;
+    }
     size_t smem = sizeof(int32_t) * (2 * (size_t)W + 2 * udp::CROP_ROWS) + (size_t)udp::CROP_ROWS * W * 3;
     if (smem > 200 * 1024) return UDP_EINVAL;
     if (smem > 48 * 1024) {
