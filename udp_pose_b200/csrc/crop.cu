@@ -223,37 +223,38 @@ __device__ __forceinline__ int q10_row(double m, double c, int y)
     return __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m, (double)y), c), 1024.0)) + 16;
 }
 
+// grid = (tile columns, persons); a CTA walks down its tile column, so everything that depends
+// only on the person and the column (matrix, Q10 column deltas, image geometry) is computed once.
 __global__ void __launch_bounds__(CT_THREADS)
 warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
-                           const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H,
-                           int tiles_x)
+                           const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H)
 {
     extern __shared__ __align__(16) unsigned char fp[];  // footprint copy
     const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
 
     const int n = blockIdx.y, t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int ty = blockIdx.x / tiles_x, tx = blockIdx.x - ty * tiles_x;
-    const int x0 = tx * CT, y0 = ty * CT;
+    const int x0 = blockIdx.x * CT;
     const float *m = M + 6 * (size_t)n;
     const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
-    // Q10 column deltas of this lane's column; Q10 row bases of one row per lane:
-    // lanes 0..7 hold this warp's rows (warp + 4*lane), lane 8 / lanes >= 9 the tile's first / last row
-    const int adx = q10_col(m00, x0 + lane), bdx = q10_col(m10, x0 + lane);
-    const int myrow = lane < 8 ? warp + 4 * lane : (lane == 8 ? 0 : CT - 1);
-    const int rX = q10_row(m01, m02, y0 + myrow), rY = q10_row(m11, m12, y0 + myrow);
+    const int adx = q10_col(m00, x0 + lane), bdx = q10_col(m10, x0 + lane);  // Q10 deltas of this lane's column
+    const int A0 = __shfl_sync(0xffffffffu, adx, 0), A1 = __shfl_sync(0xffffffffu, adx, CT - 1);
+    const int B0 = __shfl_sync(0xffffffffu, bdx, 0), B1 = __shfl_sync(0xffffffffu, bdx, CT - 1);
+    const int Amin = min(A0, A1), Amax = max(A0, A1), Bmin = min(B0, B1), Bmax = max(B0, B1);
 
     const uint8_t *src = src_ptrs[n];
     const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
     const int ssm = ss & 15;
-    const int A0 = __shfl_sync(0xffffffffu, adx, 0), A1 = __shfl_sync(0xffffffffu, adx, CT - 1);
-    const int B0 = __shfl_sync(0xffffffffu, bdx, 0), B1 = __shfl_sync(0xffffffffu, bdx, CT - 1);
-    const int Amin = min(A0, A1), Amax = max(A0, A1), Bmin = min(B0, B1), Bmax = max(B0, B1);
+    // the image buffer as 16-byte chunks: [buf, buf + lim + 16) may be read (images are < 2 GiB)
+    const char *buf = reinterpret_cast<const char *>((uintptr_t)src & ~(uintptr_t)15);
+    const int lead = (int)((uintptr_t)src & 15);
+    const bool img_ok = sh > 0 && sw > 0;
+    const unsigned lim = img_ok ? (unsigned)((((long long)(sh - 1) * ss + 3LL * sw + lead + 15) & ~15LL) - 16) : 0u;
     // per-lane constants of the 96-byte row repack: word `lane` holds bytes 4*lane .. 4*lane+3
     int p0 = min((4 * lane) / 3, 30);
     uint32_t osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
     asm volatile("" : "+r"(p0), "+r"(osel));  // keep them in registers (ptxas rematerialised them per pixel)
-    uint8_t *const out0 = dst + (((size_t)n * H + y0 + warp) * W + x0) * 3 + 4 * lane;
-    const size_t out_step = (size_t)(CT_THREADS / 32) * W * 3;
+    const size_t row_bytes = (size_t)W * 3;
+    uint8_t *out_tile = dst + ((size_t)n * H + warp) * row_bytes + (size_t)x0 * 3 + 4 * lane;  // + y0 rows below
 
     auto bbox = [&](int Xa, int Xb, int Ya, int Yb) {  // footprint of tile rows whose first/last bases are given
         TileGeom g;
@@ -264,105 +265,118 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
         g.maxc = ((30 + 3 * g.ncols) >> 4) | 1;  // 16-byte chunks per row at worst-case phase; odd count
         return g;
     };
-    auto bbox_rows = [&](int ry0, int rows) {  // (multi-pass only) recompute the two row bases
-        return bbox(q10_row(m01, m02, y0 + ry0), q10_row(m01, m02, y0 + ry0 + rows - 1),
-                    q10_row(m11, m12, y0 + ry0), q10_row(m11, m12, y0 + ry0 + rows - 1));
-    };
-    TileGeom g = bbox(__shfl_sync(0xffffffffu, rX, 8), __shfl_sync(0xffffffffu, rX, 9),
-                      __shfl_sync(0xffffffffu, rY, 8), __shfl_sync(0xffffffffu, rY, 9));
-    // rows per pass: the whole tile unless its footprint does not fit the buffer (large scale)
-    int nr = CT;
-    if (g.nrows * (g.maxc << 4) > CT_SMEM) {
-        for (nr = CT / 2; nr > 1; nr >>= 1) {
-            bool fits = true;
-            for (int ry0 = 0; ry0 < CT; ry0 += nr) {
-                const TileGeom h = bbox_rows(ry0, nr);
-                if ((long long)h.nrows * (h.maxc << 4) > CT_SMEM) { fits = false; break; }
-            }
-            if (fits) break;
-        }
-    }
 
-    for (int ry0 = 0; ry0 < CT; ry0 += nr) {
-        if (nr != CT) g = bbox_rows(ry0, nr);
-        const int pitch = g.maxc << 4;
-        const bool direct = (long long)g.nrows * pitch > CT_SMEM;  // absurd scale: per-pixel global path
-        // 16-byte phase of pixel (xa, ya); row r of the footprint has phase (shift0 + r*ssm) & 15
-        const int shift0 = (int)(((long long)(uintptr_t)src + (long long)g.ya * ss + 3LL * g.xa) & 15);
-        if (!direct) {
-            // ---- stage the footprint: 16-byte cp.async chunks, flat index = (row, chunk) = smem offset / 16.
-            // Chunk addresses are 32-bit byte offsets from the 16-byte-aligned start of the image buffer
-            // (images are < 2 GiB); a chunk is copied iff it lies inside the buffer, else zero-filled.
-            const int total = g.nrows * g.maxc;
-            const float rinv = __frcp_rn((float)g.maxc);
-            const int dr = (int)(((float)CT_THREADS + 0.5f) * rinv), dc = CT_THREADS - dr * g.maxc;
-            int r = (int)(((float)t + 0.5f) * rinv), c = t - r * g.maxc;  // exact: t, CT_THREADS << 2^20
-            const char *buf = reinterpret_cast<const char *>((uintptr_t)src & ~(uintptr_t)15);
-            const int lead = (int)((uintptr_t)src & 15);
-            const unsigned lim = sh > 0 && sw > 0 ? (unsigned)((((long long)(sh - 1) * ss + 3LL * sw + lead + 15) & ~15LL) - 16) : 0u;
-            const int base_off = lead + 3 * g.xa;  // offset of pixel (xa, row 0) from buf
-            unsigned d = fpa + ((unsigned)t << 4);
-            const long long off_lo = (long long)g.ya * ss + base_off - 15;
-            const long long off_hi = (long long)(g.ya + g.nrows - 1) * ss + base_off + pitch - 16;
-            if (g.ya >= 0 && g.ya + g.nrows <= sh && off_lo >= 0 && off_hi <= (long long)lim) {  // every chunk is in the buffer
-                for (int idx = t; idx < total; idx += CT_THREADS, d += CT_THREADS * 16) {
-                    const int off = (g.ya + r) * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
-                    r += dr; c += dc;
-                    if (c >= g.maxc) { c -= g.maxc; ++r; }
+    for (int y0 = 0; y0 < H; y0 += CT, out_tile += CT * row_bytes) {
+        // Q10 row bases, one row per lane: lanes 0..7 hold this warp's rows (warp + 4*lane),
+        // lane 8 / lanes >= 9 the tile's first / last row
+        const int myrow = lane < 8 ? warp + 4 * lane : (lane == 8 ? 0 : CT - 1);
+        const int rX = q10_row(m01, m02, y0 + myrow), rY = q10_row(m11, m12, y0 + myrow);
+        auto bbox_rows = [&](int ry0, int rows) {  // (multi-pass only) recompute the two row bases
+            return bbox(q10_row(m01, m02, y0 + ry0), q10_row(m01, m02, y0 + ry0 + rows - 1),
+                        q10_row(m11, m12, y0 + ry0), q10_row(m11, m12, y0 + ry0 + rows - 1));
+        };
+        TileGeom g = bbox(__shfl_sync(0xffffffffu, rX, 8), __shfl_sync(0xffffffffu, rX, 9),
+                          __shfl_sync(0xffffffffu, rY, 8), __shfl_sync(0xffffffffu, rY, 9));
+        // rows per pass: the whole tile unless its footprint does not fit the buffer (large scale)
+        int nr = CT;
+        if (g.nrows * (g.maxc << 4) > CT_SMEM) {
+            for (nr = CT / 2; nr > 1; nr >>= 1) {
+                bool fits = true;
+                for (int ry0 = 0; ry0 < CT; ry0 += nr) {
+                    const TileGeom h = bbox_rows(ry0, nr);
+                    if ((long long)h.nrows * (h.maxc << 4) > CT_SMEM) { fits = false; break; }
                 }
-            } else {
-                for (int idx = t; idx < total; idx += CT_THREADS, d += CT_THREADS * 16) {
-                    const int y = g.ya + r;
-                    const int off = y * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
-                    if ((unsigned)y < (unsigned)sh && (unsigned)off <= lim && sw > 0)
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
-                    else
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(d), "r"(0) : "memory");
-                    r += dr; c += dc;
-                    if (c >= g.maxc) { c -= g.maxc; ++r; }
-                }
+                if (fits) break;
             }
-            cp_async_commit();
-            cp_async_wait_all();
-            __syncthreads();
-            if (g.xa < 0 || g.xa + g.ncols > sw) {  // zero the columns left / right of the image
-                for (int rr = t; rr < g.nrows; rr += CT_THREADS) {
-                    const int y = g.ya + rr;
-                    if (y < 0 || y >= sh) continue;
-                    const int shr = (shift0 + rr * ssm) & 15;
-                    uint8_t *base = fp + rr * pitch;
-                    if (g.xa < 0) zero_bytes(base, shr, shr + 3 * min(g.ncols, -g.xa));
-                    if (g.xa + g.ncols > sw) zero_bytes(base, shr + 3 * max(0, sw - g.xa), shr + 3 * g.ncols);
+        }
+
+        for (int ry0 = 0; ry0 < CT; ry0 += nr) {
+            if (nr != CT) g = bbox_rows(ry0, nr);
+            const int pitch = g.maxc << 4;
+            const bool direct = (long long)g.nrows * pitch > CT_SMEM;  // absurd scale: per-pixel global path
+            // 16-byte phase of pixel (xa, ya); row r of the footprint has phase (shift0 + r*ssm) & 15
+            const int base_off = lead + 3 * g.xa;  // byte offset of pixel (xa, row 0) from buf
+            const int shift0 = (g.ya * ssm + base_off) & 15;
+            if (!direct) {
+                // ---- stage the footprint with 16-byte cp.async chunks that keep the global phase.
+                // nch chunks per row are copied (exact when every row has the same phase); a chunk is
+                // copied iff it lies inside the image buffer, else zero-filled.
+                const int nch = ((ssm == 0 ? shift0 : 15) + 3 * g.ncols + 15) >> 4;
+                const int total = g.nrows * nch;
+                const float rinv = __frcp_rn((float)nch);
+                const int dr = (int)(((float)CT_THREADS + 0.5f) * rinv), dc = CT_THREADS - dr * nch;
+                int r = (int)(((float)t + 0.5f) * rinv), c = t - r * nch;  // exact: t, CT_THREADS << 2^20
+                unsigned d = fpa + r * pitch + (c << 4);
+                const int dstep = dr * pitch + (dc << 4), dwrap = pitch - (nch << 4);
+                const long long off_lo = (long long)g.ya * ss + base_off - 15;
+                const long long off_hi = (long long)(g.ya + g.nrows - 1) * ss + base_off + pitch - 16;
+                if (ssm == 0 && g.ya >= 0 && g.ya + g.nrows <= sh && off_lo >= 0 && off_hi <= (long long)lim) {
+                    // every chunk is in the buffer and every row has phase shift0: pure pointer stepping
+                    const char *gp = buf + ((g.ya + r) * ss + base_off - shift0 + (c << 4));
+                    const int gstep = dr * ss + (dc << 4), gwrap = ss - (nch << 4);
+                    for (int idx = t; idx < total; idx += CT_THREADS) {
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gp) : "memory");
+                        gp += gstep; d += dstep; c += dc;
+                        if (c >= nch) { c -= nch; gp += gwrap; d += dwrap; }
+                    }
+                } else {
+                    for (int idx = t; idx < total; idx += CT_THREADS) {
+                        const int y = g.ya + r;
+                        const int off = y * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
+                        if ((unsigned)y < (unsigned)sh && (unsigned)off <= lim && img_ok)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
+                        else
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(d), "r"(0) : "memory");
+                        r += dr; d += dstep; c += dc;
+                        if (c >= nch) { c -= nch; ++r; d += dwrap; }
+                    }
                 }
+                cp_async_commit();
+                cp_async_wait_all();
                 __syncthreads();
+                if (g.xa < 0 || g.xa + g.ncols > sw) {  // zero the columns left / right of the image
+                    for (int rr = t; rr < g.nrows; rr += CT_THREADS) {
+                        const int y = g.ya + rr;
+                        if (y < 0 || y >= sh) continue;
+                        const int shr = (shift0 + rr * ssm) & 15;
+                        uint8_t *base = fp + rr * pitch;
+                        if (g.xa < 0) zero_bytes(base, shr, shr + 3 * min(g.ncols, -g.xa));
+                        if (g.xa + g.ncols > sw) zero_bytes(base, shr + 3 * max(0, sw - g.xa), shr + 3 * g.ncols);
+                    }
+                    __syncthreads();
+                }
             }
-        }
-        const int K0 = (int)fpa + shift0 - g.ya * pitch - 3 * g.xa;
-        uint8_t *outp = out0 + (size_t)ry0 * W * 3;
-        // rows of this pass owned by this warp: ry0 + warp + 4*i.  Their bases sit in lane
-        // (row - warp) / 4 when nr == CT; in multi-pass mode they are recomputed.
-#define UDP_CROP_ROWS(PIXEL_EXPR)                                                                   \
-        for (int r = ry0 + warp; r < ry0 + nr; r += CT_THREADS / 32, outp += out_step) {          \
-            int X, Y;                                                                              \
-            if (nr == CT) { X = __shfl_sync(0xffffffffu, rX, r >> 2); Y = __shfl_sync(0xffffffffu, rY, r >> 2); } \
-            else { X = q10_row(m01, m02, y0 + r); Y = q10_row(m11, m12, y0 + r); }                 \
-            X += adx; Y += bdx;                                                                    \
-            const uint32_t px = (PIXEL_EXPR);                                                      \
-            const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1); \
-            if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);        \
-        }
-        if (direct) {
-            UDP_CROP_ROWS(crop_border_pixel(src, sh, sw, ss, X, Y))
-        } else if (ssm == 0) {
+            const int K0 = (int)fpa + shift0 - g.ya * pitch - 3 * g.xa;
+            uint8_t *outp = out_tile + (size_t)ry0 * row_bytes;
+            const size_t out_step = (size_t)(CT_THREADS / 32) * row_bytes;
+            // rows of this pass owned by this warp: ry0 + warp + 4*i
+#define UDP_CROP_ROWS(ROWBASE_X, ROWBASE_Y, PIXEL_EXPR)                                              \
+            for (int r = ry0 + warp; r < ry0 + nr; r += CT_THREADS / 32, outp += out_step) {         \
+                const int X = (ROWBASE_X) + adx, Y = (ROWBASE_Y) + bdx;                               \
+                const uint32_t px = (PIXEL_EXPR);                                                     \
+                const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1); \
+                if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);       \
+            }
+            if (nr == CT && !direct) {  // the common case: row bases sit in lane (r >> 2)
+                if (ssm == 0) {
 #pragma unroll 2
-            UDP_CROP_ROWS(crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
-        } else {
+                    UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
+                                  crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
+                } else {
 #pragma unroll 2
-            UDP_CROP_ROWS(crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
-        }
+                    UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
+                                  crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
+                }
+            } else if (!direct) {       // multi-pass (large scale): row bases recomputed
+                UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
+                              crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
+            } else {
+                UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
+                              crop_border_pixel(src, sh, sw, ss, X, Y))
+            }
 #undef UDP_CROP_ROWS
-        if (ry0 + nr < CT) __syncthreads();  // the next pass overwrites the footprint buffer
+            __syncthreads();  // the next pass / tile overwrites the footprint buffer
+        }
     }
 }
 
@@ -376,12 +390,12 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
     if (N == 0) return 0;
     if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst) return UDP_EINVAL;
     if (!udp_force_generic() && W % udp::CT == 0 && H % udp::CT == 0 && ((uintptr_t)dst & 3) == 0) {
-        const int tiles_x = W / udp::CT, tiles = tiles_x * (H / udp::CT);
+        const int tiles_x = W / udp::CT;
         for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
             const int nn = N - n0 < 65535 ? N - n0 : 65535;
-            udp::warp_affine_u8_tile_kernel<<<dim3(tiles, nn), udp::CT_THREADS, udp::CT_SMEM + 16, (cudaStream_t)stream>>>(
+            udp::warp_affine_u8_tile_kernel<<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16, (cudaStream_t)stream>>>(
                 src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
-                dst + (size_t)n0 * H * W * 3, W, H, tiles_x);
+                dst + (size_t)n0 * H * W * 3, W, H);
             UDP_LAUNCH_CHECK();
         }
         return 0;
