@@ -63,6 +63,65 @@ __device__ __forceinline__ void st_stream_f4(float *p, float4 v) { __stcs(reinte
 // 16-byte read-once load (keeps L1 for the gathers that do reuse lines).
 __device__ __forceinline__ float4 ld_stream_f4(const float *p) { return __ldcs(reinterpret_cast<const float4 *>(p)); }
 
+// Packed fp32x2 values live in 64-bit registers from the moment they are formed, so ptxas keeps
+// them as aligned register pairs (holding the halves separately cost two MOVs per FFMA2 in the
+// first build of this file -- 31 % of all executed instructions were moves).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float lo_of(f32x2 v)
+{
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return a;
+}
+__device__ __forceinline__ float hi_of(f32x2 v)
+{
+    float a, b;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    return b;
+}
+__device__ __forceinline__ f32x2 ffma2p(f32x2 a, float k, f32x2 c)
+{
+    f32x2 d;
+    asm("{.reg .b64 kk;\n mov.b64 kk, {%2, %2};\n fma.rn.f32x2 %0, %1, kk, %3;}" : "=l"(d) : "l"(a), "f"(k), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 fmul2p(f32x2 a, float k)
+{
+    f32x2 d;
+    asm("{.reg .b64 kk;\n mov.b64 kk, {%2, %2};\n mul.rn.f32x2 %0, %1, kk;}" : "=l"(d) : "l"(a), "f"(k));
+    return d;
+}
+__device__ __forceinline__ f32x2 fadd2p(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 fsub2p(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 fmul2pp(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 ffma2pp(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 // center/scale loader honouring the caller's dtype.
 struct CS {
     double c0, c1;   // center as double (exact widening when float32)

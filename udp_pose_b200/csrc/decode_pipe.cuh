@@ -36,47 +36,6 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
-// Packed fp32x2 values live in 64-bit registers from the moment they are formed, so ptxas keeps
-// them as aligned register pairs (holding the halves separately cost two MOVs per FFMA2 in the
-// first build of this file -- 31 % of all executed instructions were moves).
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pk(float lo, float hi)
-{
-    f32x2 r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ float lo_of(f32x2 v)
-{
-    float a, b;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
-    return a;
-}
-__device__ __forceinline__ float hi_of(f32x2 v)
-{
-    float a, b;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
-    return b;
-}
-__device__ __forceinline__ f32x2 ffma2p(f32x2 a, float k, f32x2 c)
-{
-    f32x2 d;
-    asm("{.reg .b64 kk;\n mov.b64 kk, {%2, %2};\n fma.rn.f32x2 %0, %1, kk, %3;}" : "=l"(d) : "l"(a), "f"(k), "l"(c));
-    return d;
-}
-__device__ __forceinline__ f32x2 fmul2p(f32x2 a, float k)
-{
-    f32x2 d;
-    asm("{.reg .b64 kk;\n mov.b64 kk, {%2, %2};\n mul.rn.f32x2 %0, %1, kk;}" : "=l"(d) : "l"(a), "f"(k));
-    return d;
-}
-__device__ __forceinline__ f32x2 fadd2p(f32x2 a, f32x2 b)
-{
-    f32x2 d;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
-
 __device__ __forceinline__ float fmax3(float a, float b, float c)
 {
     float d;
