@@ -462,9 +462,19 @@ def run_ours(args):
     kern["decode"]["survey_bytes_per_person"] = ab["decode_survey"]
     kern["decode"]["frac_on_survey_bytes"] = round(ab["decode_survey"] * B / (stage_ms["decode"] * 1e-3) / 1e9 / peak, 4)
     dom = max(STAGES, key=lambda n: stage_ms[n])
+    # measured DRAM bytes of one launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, committed in
+    # profiles/traffic.json for this config and batch; scaled linearly to another batch size)
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj["cfg%d" % args.config][dom] * B / tj["persons"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": peak,
-                "unit": "GB/s", "frac": kern[dom]["frac"], "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": ab[dom] * B}
+                "unit": "GB/s", "frac": kern[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": ab[dom] * B,
+                "note": "crop reads hit L2 (64-image source pool), so DRAM traffic is below the algorithmic bytes; "
+                        "the kernel is integer-issue bound (about 55 instructions per output pixel), see DESIGN.md"}
     value = world * B * args.steps / (total_ms * 1e-3)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
