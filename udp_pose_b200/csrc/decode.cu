@@ -296,8 +296,8 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
 // maps the 32 lanes of one warp finish one mailbox entry each (first build: that tail ran on 7
 // lanes per map while the other warps waited at the next barrier -- 37 % of stall samples were
 // barrier stalls, 19 % of all instructions were the tail).
-template <int W, int H, int NT, bool POST, bool FLIP, bool DIV255>
-__global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArgs p, long long maps)
+template <int W, int H, int NT, int MINB, bool POST, bool FLIP, bool DIV255>
+__global__ void __launch_bounds__(NT, MINB) decode_gaussian_pipe_kernel(DecodeGaussArgs p, long long maps)
 {
     constexpr int R = 3;
     using G = PipeGeom<W, H, R, NT>;
@@ -342,17 +342,21 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
         }
     };
 
+    // buffer roles: bP holds out_i (then T_i), bN receives out_{i+1}; buffer 2 always holds the flipped map
     long long map = blockIdx.x;
-    int s = 0, slot = 0;
-    if (map < maps) pipe_prefetch<W, H, R, NT>(plan, 0, src_of(map), fl_of());
+    int bP = 0, bN = 1, slot = 0;
+    if (map < maps) {
+        pipe_prefetch<W, H, R, NT>(plan, bP, src_of(map));
+        if (has_fl) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+    }
     cp_async_commit();
-    for (; map < maps; map += gridDim.x, s ^= 1) {
-        float *stage = smem + s * G::STAGE;
+    for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
+        float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
         cp_async_wait_all();
-        __syncthreads();  // (A) this map has landed; the previous map's T is dead
+        __syncthreads();  // (A) this map has landed; the previous map's T (in bN) is dead
         const long long next = map + gridDim.x;
         nxt.advance();
-        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
+        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
         cp_async_commit();
         if (threadIdx.x == 0) s_idx = 0x7fffffff;
         // mailbox full: one warp finishes the 32 queued maps.  No extra barrier: the next mailbox
@@ -363,7 +367,7 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
         }
 
         f32x2 v[G::NCOL];
-        pipe_window<W, H, R, NT, FLIP, DIV255>(stage, pr, xs, v);
+        pipe_window<W, H, R, NT, FLIP, DIV255>(bufP, bufQ, pr, xs, v);
         float fs;
         const float lm = pipe_local_max<W, H, R, NT>(v, fs);
         float wm = lm;
@@ -374,17 +378,22 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
         if (__syncthreads_or(bad)) {  // a non-finite value: NaN-exact generic path for this map
             cp_async_wait_all();
             __syncthreads();
-            decode_gauss_generic_map<POST>(p, smem, map);
-            if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
+            decode_gauss_generic_map<POST>(p, smem, map);  // clobbers all three buffers
+            if (next < maps) {
+                pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
+                if (has_fl) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+            }
             cp_async_commit();
             continue;
         }
-        // (B) the raw stage is consumed (T may overwrite it) and the warp maxima are published
+        // (B) both raw buffers are consumed: T may overwrite out_i, flipped_{i+1} may land in Q
+        if (has_fl && next < maps) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+        cp_async_commit();
         float M = s_wmax[0];
 #pragma unroll
         for (int q = 1; q < NW; ++q) M = fmaxf(M, s_wmax[q]);
         if (lm == M) atomicMin(&s_idx, pipe_first_index<W, H, R, NT>(v, M, pr, xs));
-        float *T = stage;
+        float *T = bufP;
         if (POST) pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
         __syncthreads();  // (C) T complete, s_idx final
         float *box = s_box + slot * BOXW;
@@ -422,14 +431,14 @@ __global__ void __launch_bounds__(NT) decode_gaussian_pipe_kernel(DecodeGaussArg
     if (slot && warp == 0) flush(slot);
 }
 
-template <int W, int H, int NT>
+template <int W, int H, int NT, int MINB>
 static void (*pick_gauss_pipe(bool post, bool flip, bool div))(DecodeGaussArgs, long long)
 {
-#define UDP_PICK(P, F, D) if (post == P && flip == F && div == D) return decode_gaussian_pipe_kernel<W, H, NT, P, F, D>;
+#define UDP_PICK(P, F, D) if (post == P && flip == F && div == D) return decode_gaussian_pipe_kernel<W, H, NT, MINB, P, F, D>;
     UDP_PICK(true, true, false) UDP_PICK(true, false, false) UDP_PICK(true, true, true) UDP_PICK(true, false, true)
     UDP_PICK(false, true, false) UDP_PICK(false, false, false) UDP_PICK(false, true, true)
 #undef UDP_PICK
-    return decode_gaussian_pipe_kernel<W, H, NT, false, false, true>;
+    return decode_gaussian_pipe_kernel<W, H, NT, MINB, false, false, true>;
 }
 
 }  // namespace udp
@@ -470,11 +479,11 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
     // Streaming fast path: the reference's map shapes, plain or /255 (RSN) pre-scaling, no
     // blurred write-back.  Everything else (and every map holding a NaN/inf) runs the generic code.
     if (!udp_force_generic() && !blurred && (pre_div == 0.0f || pre_div == 255.0f)) {
-#define UDP_GAUSS_PIPE(WW, HH, NT)                                                               \
+#define UDP_GAUSS_PIPE(WW, HH, NT, MINB)                                                             \
         if (w == WW && h == HH) {                                                                \
             using G = udp::PipeGeom<WW, HH, 3, NT>;                                              \
             const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
-            void (*kern)(udp::DecodeGaussArgs, long long) = udp::pick_gauss_pipe<WW, HH, NT>(            \
+            void (*kern)(udp::DecodeGaussArgs, long long) = udp::pick_gauss_pipe<WW, HH, NT, MINB>(      \
                 post_process != 0, hm_flipped != nullptr, pre_div != 0.0f);                      \
             int per_sm = 0;                                                                      \
             int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
@@ -485,9 +494,9 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
             UDP_LAUNCH_CHECK();                                                                  \
             return 0;                                                                            \
         }
-        UDP_GAUSS_PIPE(48, 64, 96)
-        UDP_GAUSS_PIPE(64, 64, 128)
-        UDP_GAUSS_PIPE(72, 96, 288)
+        UDP_GAUSS_PIPE(48, 64, 96, 4)
+        UDP_GAUSS_PIPE(64, 64, 128, 3)
+        UDP_GAUSS_PIPE(72, 96, 288, 2)
 #undef UDP_GAUSS_PIPE
     }
     auto kern = post_process ? udp::decode_gaussian_kernel<true> : udp::decode_gaussian_kernel<false>;

@@ -211,8 +211,8 @@ __device__ __forceinline__ void offset_final(const DecodeOffsetArgs &p, long lon
 // share the 32 x 14 offset-window rows (scattered global loads, all in flight together), and
 // after the next barrier one warp finishes the 32 maps, one per lane.  Maps holding a
 // non-finite value are re-done by the generic path above (np.argmax's NaN rule).
-template <int W, int H, int NT, bool FLIP>
-__global__ void __launch_bounds__(NT) decode_offset_pipe_kernel(DecodeOffsetArgs p, long long maps)
+template <int W, int H, int NT, int MINB, bool FLIP>
+__global__ void __launch_bounds__(NT, MINB) decode_offset_pipe_kernel(DecodeOffsetArgs p, long long maps)
 {
     constexpr int R = 7;
     using G = PipeGeom<W, H, R, NT>;
@@ -264,17 +264,21 @@ __global__ void __launch_bounds__(NT) decode_offset_pipe_kernel(DecodeOffsetArgs
         }
     };
 
+    // buffer roles: bP holds out_i (then T_i), bN receives out_{i+1}; buffer 2 always holds the flipped map
     long long map = blockIdx.x;
-    int s = 0, slot = 0;
-    if (map < maps) pipe_prefetch<W, H, R, NT>(plan, 0, src_of(map), fl_of());
+    int bP = 0, bN = 1, slot = 0;
+    if (map < maps) {
+        pipe_prefetch<W, H, R, NT>(plan, bP, src_of(map));
+        if (FLIP) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+    }
     cp_async_commit();
-    for (; map < maps; map += gridDim.x, s ^= 1) {
-        float *stage = smem + s * G::STAGE;
+    for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
+        float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
         cp_async_wait_all();
-        __syncthreads();  // (A) this map has landed; the previous map's T is dead
+        __syncthreads();  // (A) this map has landed; the previous map's T (in bN) is dead
         const long long next = map + gridDim.x;
         nxt.advance();
-        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
+        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
         cp_async_commit();
         // mailbox full: everyone gathers offset rows now; warp 0 finishes the maps after barrier (B).
         // No extra barrier: the next mailbox / s_rows write comes after (C), resp. the next flush.
@@ -282,7 +286,7 @@ __global__ void __launch_bounds__(NT) decode_offset_pipe_kernel(DecodeOffsetArgs
         if (finish) { flush_rows(NBOX); slot = 0; }
 
         f32x2 v[G::NCOL];
-        pipe_window<W, H, R, NT, FLIP, false>(stage, pr, xs, v);
+        pipe_window<W, H, R, NT, FLIP, false>(bufP, bufQ, pr, xs, v);
         f32x2 acc = pk(0.f, 0.f);
 #pragma unroll
         for (int j = G::PAD; j < G::PAD + G::SEG; j += 2) acc = fadd2p(acc, fadd2p(v[j], v[j + 1]));
@@ -295,14 +299,19 @@ __global__ void __launch_bounds__(NT) decode_offset_pipe_kernel(DecodeOffsetArgs
             const int gn = (int)(map / p.K), gk = (int)(map - (long long)gn * p.K);
             const float *gfl = FLIP ? p.out_flipped + (((long long)gn * p.K + p.flip_perm[gk]) * 3) * (long long)hw
                                     : nullptr;
-            decode_offset_generic(p, smem, map, gn, src_of(map), gfl);
+            decode_offset_generic(p, smem, map, gn, src_of(map), gfl);  // clobbers all three buffers
             __syncthreads();
-            if (next < maps) pipe_prefetch<W, H, R, NT>(plan, s ^ 1, src_of(next), fl_of());
+            if (next < maps) {
+                pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
+                if (FLIP) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+            }
             cp_async_commit();
             continue;
         }
-        // (B) the raw stage is consumed: T may overwrite it
-        float *T = stage;
+        // (B) both raw buffers are consumed: T may overwrite out_i, flipped_{i+1} may land in Q
+        if (FLIP && next < maps) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+        cp_async_commit();
+        float *T = bufP;
         pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
         __syncthreads();  // (C) T complete
         float v0 = -INFINITY, v1 = -INFINITY;
@@ -354,13 +363,13 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
     size_t gsmem = udp::BlurGeom<7>::smem_floats(w, h) * sizeof(float);
     if (gsmem > 200 * 1024) return UDP_EINVAL;
     if (!udp_force_generic()) {
-#define UDP_OFF_PIPE(WW, HH, NT)                                                                 \
+#define UDP_OFF_PIPE(WW, HH, NT, MINB)                                                               \
         if (w == WW && h == HH) {                                                                \
             using G = udp::PipeGeom<WW, HH, 7, NT>;                                              \
             const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
             void (*kern)(udp::DecodeOffsetArgs, long long) =                                     \
-                out_flipped ? udp::decode_offset_pipe_kernel<WW, HH, NT, true>                   \
-                            : udp::decode_offset_pipe_kernel<WW, HH, NT, false>;                 \
+                out_flipped ? udp::decode_offset_pipe_kernel<WW, HH, NT, MINB, true>             \
+                            : udp::decode_offset_pipe_kernel<WW, HH, NT, MINB, false>;           \
             int per_sm = 0;                                                                      \
             int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
             if (rc) return rc;                                                                   \
@@ -370,9 +379,9 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
             UDP_LAUNCH_CHECK();                                                                  \
             return 0;                                                                            \
         }
-        UDP_OFF_PIPE(48, 64, 96)
-        UDP_OFF_PIPE(64, 64, 128)
-        UDP_OFF_PIPE(72, 96, 288)
+        UDP_OFF_PIPE(48, 64, 96, 4)
+        UDP_OFF_PIPE(64, 64, 128, 3)
+        UDP_OFF_PIPE(72, 96, 288, 2)
 #undef UDP_OFF_PIPE
     }
     cudaError_t e = cudaFuncSetAttribute(udp::decode_offset_kernel,

@@ -6,18 +6,21 @@
 // 36-48 % issue-active, 20-30 % of DRAM peak), and ~8000 warp-instructions per 64x48 map.
 //
 // This version:
-//  * persistent CTAs (a few per SM) walk the (person, joint) maps with a 2-stage cp.async
-//    pipeline: while map i is being decoded, the 16-byte asynchronous copies of map i+1 (and
-//    of its mirrored partner map) are already in flight into the other stage.  The copies
-//    place each row at a padded stride (SR/4 odd) so that the later per-row LDS.128 reads are
-//    bank-conflict free; no thread ever holds HBM data in registers while waiting.
+//  * persistent CTAs (a few per SM) walk the (person, joint) maps with a cp.async pipeline:
+//    while map i is being decoded, the 16-byte asynchronous copies of map i+1 (and of its
+//    mirrored partner map) are already in flight.  Three buffers rotate: P holds out_i and,
+//    once the row pass has consumed it, T_i; Q holds flipped_i and is refilled with
+//    flipped_{i+1} as soon as the row pass has read it; N receives out_{i+1} and becomes the
+//    next P.  The copies place each row at a padded stride (SR/4 odd) so that the later per-row
+//    LDS.128 reads are bank-conflict free; no thread holds HBM data in registers while waiting.
 //  * the flip test ((out + mirror(partner)) * 0.5, utils/transforms.py:15-47 +
 //    core/function.py:171) is fused into the ROW pass: a thread owns two rows (p, p + H/2) and a
 //    column segment, averages its window straight into row-paired registers and runs cv2's
 //    left-to-right FMA chain with packed fma.rn.f32x2 -- the padded copy A2 of the first
 //    generation, its store/load round trip and one barrier are gone.
-//  * T (the row-pass result, with reflected halo rows) aliases the stage the map came from,
-//    so shared memory is just the two stages.
+//  * T (the row-pass result, with reflected halo rows) aliases the buffer out_i came from, so
+//    shared memory is three map-sized buffers (four in the first build of this file, which
+//    limited the 96x72 maps to one CTA per SM).
 //  * the column pass pairs two COLUMNS (x, x+1), cv2's centre-then-symmetric-pairs order.
 //  * the raw arg-max needs only FMNMX per element: block max first, then the (rare) threads
 //    whose local max equals it rescan their registers for the first index.
@@ -82,8 +85,8 @@ struct PipeGeom {
     static constexpr int ST = W + 2;                      // T row stride
     static constexpr int TROWS = H + 2 * R;
     static constexpr int RAW = H * SR;                    // floats per raw tensor
-    static constexpr int STAGE = (2 * RAW > TROWS * ST) ? 2 * RAW : ((TROWS * ST + 3) / 4) * 4;
-    static constexpr size_t SMEM = (size_t)2 * STAGE * sizeof(float);
+    static constexpr int BUF = (RAW > TROWS * ST) ? RAW : ((TROWS * ST + 3) / 4) * 4;  // one buffer
+    static constexpr size_t SMEM = (size_t)3 * BUF * sizeof(float);
     static constexpr int NWARP = (NT + 31) / 32;
 };
 
@@ -100,7 +103,7 @@ struct PipePlan {
     static constexpr int RPI = NT / W4;  // rows per iteration
     static_assert(H % RPI == 0, "H must be a multiple of NT/(W/4)");
     static constexpr int ITER = H / RPI;
-    unsigned dst;  // shared-space byte address inside stage 0
+    unsigned dst;  // shared-space byte address inside buffer 0
     unsigned src;  // float offset inside the map
     __device__ __forceinline__ void init(const float *smem_base)
     {
@@ -110,25 +113,18 @@ struct PipePlan {
     }
 };
 
+// one tensor (H x W floats at `src`) -> buffer `buf` (0..2), rows at stride SR
 template <int W, int H, int R, int NT>
-__device__ __forceinline__ void pipe_prefetch(const PipePlan<W, H, R, NT> &pl, int stage,
-                                              const float *__restrict__ src, const float *__restrict__ fl)
+__device__ __forceinline__ void pipe_prefetch(const PipePlan<W, H, R, NT> &pl, int buf, const float *__restrict__ src)
 {
     using G = PipeGeom<W, H, R, NT>;
     using P = PipePlan<W, H, R, NT>;
-    const unsigned d0 = pl.dst + (unsigned)stage * (unsigned)(G::STAGE * 4);
+    const unsigned d0 = pl.dst + (unsigned)buf * (unsigned)(G::BUF * 4);
     const float *s0 = src + pl.src;
 #pragma unroll
     for (int j = 0; j < P::ITER; ++j)
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + (unsigned)(j * P::RPI * G::SR * 4)),
                      "l"(s0 + j * NT * 4) : "memory");
-    if (fl) {
-        const float *f0 = fl + pl.src;
-#pragma unroll
-        for (int j = 0; j < P::ITER; ++j)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + (unsigned)((G::RAW + j * P::RPI * G::SR) * 4)),
-                         "l"(f0 + j * NT * 4) : "memory");
-    }
 }
 
 // (person, joint) of a map index that advances by a fixed step, without 64-bit divisions.
@@ -150,14 +146,14 @@ struct MapWalk {
 // The averaged window of one thread: v[j] = (row p, row p + HP) at column x0 - PAD + j.
 // mode: 0 = no flip, 1 = flip (+), 2 = flip with the partner negated (x-offset channels).
 template <int W, int H, int R, int NT, bool FLIP, bool DIV255>
-__device__ __forceinline__ void pipe_window(const float *stage, int p, int xs,
+__device__ __forceinline__ void pipe_window(const float *raw_out, const float *raw_fl, int p, int xs,
                                             f32x2 (&v)[PipeGeom<W, H, R, NT>::NCOL])
 {
     using G = PipeGeom<W, H, R, NT>;
     constexpr int PAD = G::PAD, SEG = G::SEG;
     const int x0 = xs * SEG;
-    const float *a0 = stage + p * G::SR, *a1 = a0 + G::HP * G::SR;
-    const float *f0 = a0 + G::RAW, *f1 = a1 + G::RAW;
+    const float *a0 = raw_out + p * G::SR, *a1 = a0 + G::HP * G::SR;
+    const float *f0 = raw_fl + p * G::SR, *f1 = f0 + G::HP * G::SR;
 #pragma unroll
     for (int q = 0; q < G::NV4; ++q) {
         int xc = x0 - PAD + 4 * q;
