@@ -357,22 +357,26 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
                 const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1); \
                 if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);       \
             }
-            if (nr == CT && !direct) {  // the common case: row bases sit in lane (r >> 2)
-                if (ssm == 0) {
-#pragma unroll 2
-                    UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
-                                  crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
+            // the Q10 bases of row r sit in lane (r - warp) / 4 == r >> 2 of this warp (passes of >= 4 rows)
+            if (nr < 4) {  // absurd scale: 1 or 2 rows per pass, bases recomputed
+                if (direct) {
+                    UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
+                                  crop_border_pixel(src, sh, sw, ss, X, Y))
                 } else {
-#pragma unroll 2
-                    UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
+                    UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
                                   crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
                 }
-            } else if (!direct) {       // multi-pass (large scale): row bases recomputed
-                UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
-                              crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
-            } else {
-                UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
+            } else if (direct) {
+                UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
                               crop_border_pixel(src, sh, sw, ss, X, Y))
+            } else if (ssm == 0) {
+#pragma unroll 2
+                UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
+                              crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
+            } else {
+#pragma unroll 2
+                UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
+                              crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
             }
 #undef UDP_CROP_ROWS
             __syncthreads();  // the next pass / tile overwrites the footprint buffer
