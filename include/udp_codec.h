@@ -9,6 +9,8 @@
  *
  * Conventions
  *  - every pointer is a DEVICE pointer unless the comment says HOST; row-major, dense;
+ *    float map tensors (targets, network outputs, blurred) must be 16-byte aligned (UDP_EINVAL
+ *    otherwise) -- any tensor that starts an allocation is;
  *  - `stream` is a cudaStream_t (NULL = default stream); calls are asynchronous;
  *  - return value: 0 on success, otherwise a cudaError_t (> 0) or UDP_EINVAL (< 0);
  *    no exceptions cross the ABI, nothing is allocated, nothing is synchronised;

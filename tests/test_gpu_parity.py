@@ -305,3 +305,58 @@ def test_crop_generic_path_matches_tiled(impl):
     finally:
         del os.environ["UDP_FORCE_GENERIC"]
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("cid", [1, 2])
+def test_decode_generic_and_misaligned_match_streaming(impl, cid):
+    """UDP_FORCE_GENERIC=1 routes the decoders through the shape-generic kernels: identical bits.
+    Map tensors must be 16-byte aligned (vector loads): a misaligned one is rejected, not misread."""
+    import os
+    import torch
+    from udp_pose_b200 import device_api as D
+    cfg = CONFIGS[cid]
+    rng = np.random.default_rng(60 + cid)
+    N = 9
+    out, fl = synth.heatmaps(cfg, N, rng)
+    c, s, _ = synth.boxes(cfg, N, rng)
+    a = D.decode_batch(cfg, out, fl, c, s, want_idx=True)
+    os.environ["UDP_FORCE_GENERIC"] = "1"
+    try:
+        b = D.decode_batch(cfg, out, fl, c, s, want_idx=True)
+    finally:
+        del os.environ["UDP_FORCE_GENERIC"]
+    def shifted(x):  # same values at an address that is only 4-byte aligned
+        buf = torch.empty(x.size + 1, dtype=torch.float32, device="cuda")
+        buf[1:] = torch.from_numpy(x.reshape(-1)).cuda()
+        v = buf[1:].view(*x.shape)
+        assert v.data_ptr() % 16 != 0
+        return v
+    from udp_pose_b200._lib import UdpCodecError
+    with pytest.raises(UdpCodecError):
+        D.decode_batch(cfg, shifted(out), shifted(fl), c, s, want_idx=True)
+    for k in ("preds", "maxvals", "preds_in", "idx"):
+        assert torch.equal(a[k], b[k]), k
+
+
+def test_decode_nonfinite_maps_inside_a_stream(impl, orc):
+    """A NaN / inf map in the middle of a batch is re-done by the NaN-exact generic path inside the
+    persistent kernel; its neighbours (prefetched while it ran) must be unaffected."""
+    cfg = CONFIGS[1]
+    rng = np.random.default_rng(71)
+    N = 40
+    out, fl = synth.heatmaps(cfg, N, rng)
+    out[3, 5, 10, 7] = np.nan
+    out[3, 6, 0, 0] = np.inf
+    out[17, 0, 63, 47] = -np.inf
+    fl[29, 16, 1, 1] = np.nan
+    c, s, _ = synth.boxes(cfg, N, rng)
+    with np.errstate(all="ignore"):
+        a = orc.decode(cfg, out, fl, c, s)
+    b = impl.decode(cfg, out, fl, c, s)
+    assert np.array_equal(a["idx"], b["idx"])
+    nan = np.isnan(a["maxvals"])                         # NaN payload/sign bits are not part of the contract
+    assert np.array_equal(nan, np.isnan(b["maxvals"])) and nan.sum() == 2
+    assert same_bits(a["maxvals"][~nan], b["maxvals"][~nan])
+    assert np.array_equal(np.isnan(a["preds"]), np.isnan(b["preds"]))
+    ok = ~np.isnan(a["preds"])
+    assert np.abs(a["preds"][ok] - b["preds"][ok]).max() <= 1e-4

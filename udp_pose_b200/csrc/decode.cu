@@ -449,6 +449,7 @@ extern "C" int udp_flip_back(const float *out, const float *flipped, const int32
     if (N < 0 || K < 1 || w < 4 || (w & 3) || h < 1) return UDP_EINVAL;
     if (N == 0) return 0;
     if (!flipped || !flip_perm || !dst || dst == flipped) return UDP_EINVAL;
+    if ((((uintptr_t)out | (uintptr_t)flipped | (uintptr_t)dst) & 15) != 0) return UDP_EINVAL;
     long long total4 = (long long)N * K * (triplets ? 3 : 1) * h * (w >> 2);
     long long blocks = (total4 + 255) / 256;
     if (blocks > 148 * 32) blocks = 148 * 32;
@@ -469,6 +470,7 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
     if (!hm || !preds || !maxvals || (hm_flipped && !flip_perm) || ((center == nullptr) != (scale == nullptr)))
         return UDP_EINVAL;
     if (blurred && !post_process) return UDP_EINVAL;
+    if ((((uintptr_t)hm | (uintptr_t)hm_flipped | (uintptr_t)blurred) & 15) != 0) return UDP_EINVAL;  // 16-byte vector access
     udp::DecodeGaussArgs a{hm, hm_flipped, flip_perm, center, scale, cs_f64, pre_div, K, w, h,
                            preds, maxvals, preds_in, argmax_idx, packed, blurred};
     long long maps = (long long)N * K;

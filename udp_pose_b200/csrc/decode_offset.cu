@@ -356,6 +356,7 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
     if (N == 0) return 0;
     if (!out || !preds || !maxvals || (out_flipped && !flip_perm) || ((center == nullptr) != (scale == nullptr)))
         return UDP_EINVAL;
+    if ((((uintptr_t)out | (uintptr_t)out_flipped) & 15) != 0) return UDP_EINVAL;  // 16-byte vector access
     udp::DecodeOffsetArgs a{out, out_flipped, flip_perm, (float)kpd, center, scale, cs_f64, K, w, h,
                             preds, maxvals, preds_in, argmax_idx, packed};
     long long maps = (long long)N * K;
