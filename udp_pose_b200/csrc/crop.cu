@@ -256,27 +256,24 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
     const size_t row_bytes = (size_t)W * 3;
     uint8_t *out_tile = dst + ((size_t)n * H + warp) * row_bytes + (size_t)x0 * 3 + 4 * lane;  // + y0 rows below
 
-    auto bbox = [&](int Xa, int Xb, int Ya, int Yb) {  // footprint of tile rows whose first/last bases are given
+    // Q10 row bases of the whole tile column, once per CTA (float64 products, as OpenCV rounds them)
+    int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + 16);
+    for (int y = t; y < H; y += CT_THREADS) rowq[y] = make_int2(q10_row(m01, m02, y), q10_row(m11, m12, y));
+    __syncthreads();
+
+    auto bbox = [&](int2 qa, int2 qb) {  // footprint of the tile rows whose first / last bases are given
         TileGeom g;
-        g.xa = (min(Xa, Xb) + Amin) >> 10;
-        g.ya = (min(Ya, Yb) + Bmin) >> 10;
-        g.ncols = ((max(Xa, Xb) + Amax) >> 10) + 2 - g.xa;
-        g.nrows = ((max(Ya, Yb) + Bmax) >> 10) + 2 - g.ya;
+        g.xa = (min(qa.x, qb.x) + Amin) >> 10;
+        g.ya = (min(qa.y, qb.y) + Bmin) >> 10;
+        g.ncols = ((max(qa.x, qb.x) + Amax) >> 10) + 2 - g.xa;
+        g.nrows = ((max(qa.y, qb.y) + Bmax) >> 10) + 2 - g.ya;
         g.maxc = ((30 + 3 * g.ncols) >> 4) | 1;  // 16-byte chunks per row at worst-case phase; odd count
         return g;
     };
 
     for (int y0 = 0; y0 < H; y0 += CT, out_tile += CT * row_bytes) {
-        // Q10 row bases, one row per lane: lanes 0..7 hold this warp's rows (warp + 4*lane),
-        // lane 8 / lanes >= 9 the tile's first / last row
-        const int myrow = lane < 8 ? warp + 4 * lane : (lane == 8 ? 0 : CT - 1);
-        const int rX = q10_row(m01, m02, y0 + myrow), rY = q10_row(m11, m12, y0 + myrow);
-        auto bbox_rows = [&](int ry0, int rows) {  // (multi-pass only) recompute the two row bases
-            return bbox(q10_row(m01, m02, y0 + ry0), q10_row(m01, m02, y0 + ry0 + rows - 1),
-                        q10_row(m11, m12, y0 + ry0), q10_row(m11, m12, y0 + ry0 + rows - 1));
-        };
-        TileGeom g = bbox(__shfl_sync(0xffffffffu, rX, 8), __shfl_sync(0xffffffffu, rX, 9),
-                          __shfl_sync(0xffffffffu, rY, 8), __shfl_sync(0xffffffffu, rY, 9));
+        auto bbox_rows = [&](int ry0, int rows) { return bbox(rowq[y0 + ry0], rowq[y0 + ry0 + rows - 1]); };
+        TileGeom g = bbox_rows(0, CT);
         // rows per pass: the whole tile unless its footprint does not fit the buffer (large scale)
         int nr = CT;
         if (g.nrows * (g.maxc << 4) > CT_SMEM) {
@@ -302,33 +299,33 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
                 // nch chunks per row are copied (exact when every row has the same phase); a chunk is
                 // copied iff it lies inside the image buffer, else zero-filled.
                 const int nch = ((ssm == 0 ? shift0 : 15) + 3 * g.ncols + 15) >> 4;
-                const int total = g.nrows * nch;
-                const float rinv = __frcp_rn((float)nch);
-                const int dr = (int)(((float)CT_THREADS + 0.5f) * rinv), dc = CT_THREADS - dr * nch;
-                int r = (int)(((float)t + 0.5f) * rinv), c = t - r * nch;  // exact: t, CT_THREADS << 2^20
-                unsigned d = fpa + r * pitch + (c << 4);
-                const int dstep = dr * pitch + (dc << 4), dwrap = pitch - (nch << 4);
-                const long long off_lo = (long long)g.ya * ss + base_off - 15;
-                const long long off_hi = (long long)(g.ya + g.nrows - 1) * ss + base_off + pitch - 16;
-                if (ssm == 0 && g.ya >= 0 && g.ya + g.nrows <= sh && off_lo >= 0 && off_hi <= (long long)lim) {
+                // a row goes to a group of G = 2^lg lanes (one chunk per lane), 32/G rows per warp per
+                // turn: no index division, and every lane's pointers advance by constants
+                const int lg = nch > 16 ? 5 : 32 - __clz(nch - 1);  // smallest G >= nch, G <= 32
+                const int c0 = lane & ((1 << lg) - 1), r0 = (warp << (5 - lg)) + (lane >> lg);
+                const int rstep = (CT_THREADS / 32) << (5 - lg);
+                const bool rows_in = g.ya >= 0 && g.ya + g.nrows <= sh;
+                const int off0 = g.ya * ss + base_off;  // pixel (xa, ya); fits: images are < 2 GiB
+                if (ssm == 0 && rows_in && off0 - 15 >= 0 && (unsigned)(off0 + (g.nrows - 1) * ss + pitch - 16) <= lim) {
                     // every chunk is in the buffer and every row has phase shift0: pure pointer stepping
-                    const char *gp = buf + ((g.ya + r) * ss + base_off - shift0 + (c << 4));
-                    const int gstep = dr * ss + (dc << 4), gwrap = ss - (nch << 4);
-                    for (int idx = t; idx < total; idx += CT_THREADS) {
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gp) : "memory");
-                        gp += gstep; d += dstep; c += dc;
-                        if (c >= nch) { c -= nch; gp += gwrap; d += dwrap; }
+                    for (int c = c0; c < nch; c += 32) {
+                        const char *gp = buf + (off0 + r0 * ss - shift0 + (c << 4));
+                        unsigned d = fpa + r0 * pitch + (c << 4);
+                        const int gstep = rstep * ss, dstep = rstep * pitch;
+                        for (int r = r0; r < g.nrows; r += rstep, gp += gstep, d += dstep)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gp) : "memory");
                     }
                 } else {
-                    for (int idx = t; idx < total; idx += CT_THREADS) {
-                        const int y = g.ya + r;
-                        const int off = y * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
-                        if ((unsigned)y < (unsigned)sh && (unsigned)off <= lim && img_ok)
-                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
-                        else
-                            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(d), "r"(0) : "memory");
-                        r += dr; d += dstep; c += dc;
-                        if (c >= nch) { c -= nch; ++r; d += dwrap; }
+                    for (int c = c0; c < nch; c += 32) {
+                        for (int r = r0; r < g.nrows; r += rstep) {
+                            const int y = g.ya + r;
+                            const int off = y * ss + base_off - ((shift0 + r * ssm) & 15) + (c << 4);
+                            const unsigned d = fpa + r * pitch + (c << 4);
+                            if ((unsigned)y < (unsigned)sh && (unsigned)off <= lim && img_ok)
+                                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(buf + off) : "memory");
+                            else
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};\n" ::"r"(d), "r"(0) : "memory");
+                        }
                     }
                 }
                 cp_async_commit();
@@ -349,34 +346,23 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
             const int K0 = (int)fpa + shift0 - g.ya * pitch - 3 * g.xa;
             uint8_t *outp = out_tile + (size_t)ry0 * row_bytes;
             const size_t out_step = (size_t)(CT_THREADS / 32) * row_bytes;
-            // rows of this pass owned by this warp: ry0 + warp + 4*i
-#define UDP_CROP_ROWS(ROWBASE_X, ROWBASE_Y, PIXEL_EXPR)                                              \
+            // rows of this pass owned by this warp: ry0 + warp + 4*i; their Q10 bases come from rowq
+#define UDP_CROP_ROWS(PIXEL_EXPR)                                                                     \
             for (int r = ry0 + warp; r < ry0 + nr; r += CT_THREADS / 32, outp += out_step) {         \
-                const int X = (ROWBASE_X) + adx, Y = (ROWBASE_Y) + bdx;                               \
+                const int2 q = rowq[y0 + r];                                                          \
+                const int X = q.x + adx, Y = q.y + bdx;                                               \
                 const uint32_t px = (PIXEL_EXPR);                                                     \
                 const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1); \
                 if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);       \
             }
-            // the Q10 bases of row r sit in lane (r - warp) / 4 == r >> 2 of this warp (passes of >= 4 rows)
-            if (nr < 4) {  // absurd scale: 1 or 2 rows per pass, bases recomputed
-                if (direct) {
-                    UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
-                                  crop_border_pixel(src, sh, sw, ss, X, Y))
-                } else {
-                    UDP_CROP_ROWS(q10_row(m01, m02, y0 + r), q10_row(m11, m12, y0 + r),
-                                  crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
-                }
-            } else if (direct) {
-                UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
-                              crop_border_pixel(src, sh, sw, ss, X, Y))
+            if (direct) {  // absurd scale: per-pixel global path
+                UDP_CROP_ROWS(crop_border_pixel(src, sh, sw, ss, X, Y))
             } else if (ssm == 0) {
 #pragma unroll 2
-                UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
-                              crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
+                UDP_CROP_ROWS(crop_tile_pixel<true>(X, Y, pitch, K0, shift0, g.ya, 0))
             } else {
 #pragma unroll 2
-                UDP_CROP_ROWS(__shfl_sync(0xffffffffu, rX, r >> 2), __shfl_sync(0xffffffffu, rY, r >> 2),
-                              crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
+                UDP_CROP_ROWS(crop_tile_pixel<false>(X, Y, pitch, K0, shift0, g.ya, ssm))
             }
 #undef UDP_CROP_ROWS
             __syncthreads();  // the next pass / tile overwrites the footprint buffer
@@ -393,11 +379,11 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
     if (N < 0 || W < 1 || H < 1 || (W & 1)) return UDP_EINVAL;
     if (N == 0) return 0;
     if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst) return UDP_EINVAL;
-    if (!udp_force_generic() && W % udp::CT == 0 && H % udp::CT == 0 && ((uintptr_t)dst & 3) == 0) {
+    if (!udp_force_generic() && W % udp::CT == 0 && H % udp::CT == 0 && H <= 1024 && ((uintptr_t)dst & 3) == 0) {
         const int tiles_x = W / udp::CT;
         for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
             const int nn = N - n0 < 65535 ? N - n0 : 65535;
-            udp::warp_affine_u8_tile_kernel<<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16, (cudaStream_t)stream>>>(
+            udp::warp_affine_u8_tile_kernel<<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, (cudaStream_t)stream>>>(
                 src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
                 dst + (size_t)n0 * H * W * 3, W, H);
             UDP_LAUNCH_CHECK();
