@@ -485,7 +485,7 @@ def run_ours(args):
                        "l2": "inputs larger than L2 (%.1f GB of network outputs per step per GPU)" % (2 * cfg.channels * h * w * 4 * B / 1e9)},
             "roofline": roofline, "kernels": kern,
             "gather_ms": round(stage_ms["gather"], 4),
-            "gpu_launches": len(STAGES) * args.steps,
+            "gpu_launches": (len(STAGES) - 1 + D.crop_launches(cfg.image_size)) * args.steps,
             "clocks": clocks}
     if e2e:
         line["e2e"] = e2e

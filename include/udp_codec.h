@@ -46,10 +46,15 @@ int udp_warp_matrices(const void *center, const void *scale, int cs_f64, const d
  *     call sites JointsDataset.py:227, RSN/dataset/JointsDataset.py:197-198.
  *     src_ptrs [N] device array of device pointers (one image per person, may repeat);
  *     src_h/src_w/src_stride [N] int32 (stride in bytes).  dst [N,H,W,3] uint8.
- *     Bit-exact with OpenCV's fixed-point path (Q10 coordinates, Q5 fractions, Q15 weights). */
+ *     Bit-exact with OpenCV's fixed-point path (Q10 coordinates, Q5 fractions, Q15 weights).
+ *     Images whose stride is a multiple of 16 bytes are fetched by the TMA unit (one tensor load
+ *     per 32 x {32,16,8} output tile, hardware zero fill outside the image); any other stride /
+ *     alignment works through a cp.async path.  udp_warp_affine_launches() = kernel launches
+ *     one call makes for this crop size (2 when both paths are armed, else 1). */
 int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                        const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H,
                        int N, void *stream);
+int udp_warp_affine_launches(int W, int H);
 
 /* a3  rotate_points(joints[:, 0:2], r, c, image_size, s, do_clip)  JointsDataset.py:51-73, call :228.
  *     joints [N,K,jstride] float64 (x,y at 0,1), out [N,K,ostride] float64; may alias. */

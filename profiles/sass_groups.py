@@ -4,7 +4,10 @@ import csv, subprocess, sys
 rep = sys.argv[1]; thr = float(sys.argv[2]) if len(sys.argv) > 2 else 3.0
 out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-hi = next(i for i, r in enumerate(rows) if r and r[0] == 'Address')
+his = [i for i, r in enumerate(rows) if r and r[0] == 'Address'] + [len(rows)]
+import os
+kidx = int(os.environ.get('NCU_KERNEL', '0'))  # which kernel of a multi-kernel report
+hi = his[kidx]; rows = rows[:his[kidx + 1]]
 h = rows[hi]; iS = h.index('Source'); iE = h.index('Instructions Executed')
 body = [r for r in rows[hi + 1:] if len(r) > iE and r[iE] != '']
 grp = []

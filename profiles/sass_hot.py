@@ -4,11 +4,14 @@ import csv, subprocess, sys, collections
 rep = sys.argv[1]
 out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-hi = next(i for i, r in enumerate(rows) if r and r[0] == 'Address')
+his = [i for i, r in enumerate(rows) if r and r[0] == 'Address'] + [len(rows)]
+import os
+kidx = int(os.environ.get('NCU_KERNEL', '0'))  # which kernel of a multi-kernel report
+hi = his[kidx]; rows = rows[:his[kidx + 1]]
 h = rows[hi]
 iS, iE, iW = h.index('Source'), h.index('Instructions Executed'), h.index('Warp Stall Sampling (All Samples)')
 stalls = [c for c in h if c.startswith('stall_') and 'Not Issued' not in c]
-body = [r for r in rows[hi + 1:] if len(r) > iW and r[iE] != '']
+body = [r for r in rows[hi + 1:] if len(r) > max(iW, iE) and r[iE] != '']
 tot = sum(int(r[iE]) for r in body); tots = sum(int(r[iW]) for r in body)
 print('instructions executed', tot, 'stall samples', tots)
 ops = collections.Counter(); 

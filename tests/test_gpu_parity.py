@@ -287,6 +287,58 @@ def test_crop_alignment_and_edges(impl, orc, case):
         assert got.max() == 0
 
 
+@pytest.mark.parametrize("cid", [2, 3])
+def test_crop_tma_and_cpasync_paths_agree(impl, orc, cid):
+    """Images with a 16-byte stride go through the TMA kernel (device-patched tensor map, hardware
+    zero fill), the rest through the cp.async kernel; UDP_CROP_NO_TMA=1 forces the latter for all.
+    Same bytes from both, and from the oracle on a subset.  Covers: contiguous 640-wide images,
+    a padded pitch with garbage in the padding, a misaligned base with an aligned pitch (the
+    bytes before the first pixel are not zero-filled by TMA), a stride that is not a multiple of 16,
+    every tile height (scales up to 3.3), rotated and unrotated boxes crossing all four edges."""
+    import os
+    import torch
+    from udp_pose_b200 import device_api as D
+    cfg = CONFIGS[cid]
+    W, H = cfg.image_size
+    rng = np.random.default_rng(100 + cid)
+    N = 384
+    hw = [(480, 640), (300, 401), (360, 638), (375, 500)]
+    imgs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in hw]
+    dev = [torch.from_numpy(imgs[0]).cuda()]
+    pad = torch.full((300, 1216), 255, dtype=torch.uint8, device="cuda")          # pitch 1216 = 16 * 76 > 3 * 401
+    pad[:, :1203] = torch.from_numpy(imgs[1].reshape(300, 1203)).cuda()
+    dev.append(pad.as_strided((300, 401, 3), (1216, 3, 1)))
+    buf = torch.full((360 * 1920 + 64,), 255, dtype=torch.uint8, device="cuda")  # base + 3, pitch 1920
+    inner = buf[3:3 + 360 * 1920].view(360, 1920)
+    inner[:, :1914] = torch.from_numpy(imgs[2].reshape(360, 1914)).cuda()
+    dev.append(inner.as_strided((360, 638, 3), (1920, 3, 1)))
+    assert dev[2].data_ptr() % 16 == 3
+    dev.append(torch.from_numpy(imgs[3]).cuda())                                  # stride 1500: cp.async path
+    idx = np.arange(N) % 4
+    c = np.zeros((N, 2), np.float32)
+    s = np.zeros((N, 2), np.float32)
+    r = np.where(rng.uniform(size=N) < 0.4, 0.0, np.clip(rng.standard_normal(N) * 40, -80, 80))
+    for i in range(N):
+        h, w = hw[idx[i]]
+        bh = rng.uniform(0.2, 1.4) * h * (H / 256.0) ** 0 if i % 7 else rng.uniform(1.4, 1.8) * h
+        s[i] = np.array([bh * W / H, bh]) / 200.0 * 1.25
+        c[i] = [rng.uniform(-0.15, 1.15) * w, rng.uniform(-0.15, 1.15) * h]
+    M = orc.warp_matrices(r, c, s, W, H)
+    src = D.SourceImages(dev, idx)
+    assert D.crop_launches((W, H)) == 2
+    a = D.crop_batch(src, M, (W, H))
+    os.environ["UDP_CROP_NO_TMA"] = "1"
+    try:
+        assert D.crop_launches((W, H)) == 1
+        b = D.crop_batch(src, M, (W, H))
+    finally:
+        del os.environ["UDP_CROP_NO_TMA"]
+    assert torch.equal(a, b)
+    got = a.cpu().numpy()
+    for i in range(0, N, 5):
+        assert np.array_equal(orc.O.warp_affine_u8(imgs[idx[i]], M[i], W, H), got[i]), i
+
+
 def test_crop_generic_path_matches_tiled(impl):
     """UDP_FORCE_GENERIC=1 routes the crop through the first-generation kernel: same bytes."""
     import os

@@ -16,6 +16,7 @@ SIGNATURES = {
     "udp_codec_sm_arch": [],
     "udp_warp_matrices": [_vp, _vp, _i, _vp, _i, _i, _vp, _i, _vp],
     "udp_warp_affine_u8": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "udp_warp_affine_launches": [_i, _i],
     "udp_rotate_points": [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _i, _i, _i, _vp],
     "udp_rsn_transform_joints": [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp],
     "udp_encode_gaussian": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _d, _vp, _vp, _i, _vp],

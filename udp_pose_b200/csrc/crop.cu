@@ -14,6 +14,9 @@
 // rint(M00*x*1024), rint(M10*x*1024) and the per-row bases are float64 and are computed
 // once per CTA into shared memory; the per-pixel work is integer only.  The finished
 // ROWS x W x 3 byte tile is staged in shared memory and leaves as 16-byte streaming stores.
+#include <cuda.h>  // CUtensorMap and its enums (types only: the encoder is fetched with cudaGetDriverEntryPoint)
+#include <mutex>
+
 #include "decode_pipe.cuh"
 
 namespace udp {
@@ -217,6 +220,76 @@ __device__ __forceinline__ uint32_t crop_tile_pixel(int X, int Y, int pitch, int
     return __byte_perm(__byte_perm(Sr << 6, Sg << 6, 0x4462), Sb << 6, 0x4610);
 }
 
+// The same pixel in two halves, so that a caller can put the loads of the next row in front of
+// the arithmetic of the current one (uniform 16-byte phase only: pitch % 16 == 0).
+struct CropTaps {
+    uint32_t u0, u1, u2, v0, v1, v2, h0, fxy;
+};
+__device__ __forceinline__ CropTaps crop_tile_load(int X, int Y, int pitch, int K0)
+{
+    CropTaps tp;
+    const int sx = X >> 10, sy = Y >> 10;
+    tp.fxy = (((uint32_t)X >> 5) & 31u) | (((uint32_t)Y << 11) & 0x1f0000u);  // fx | fy << 16
+    const int a0 = sy * pitch + (3 * sx + K0);
+    const unsigned q0 = (unsigned)a0 & ~3u, q1 = q0 + (unsigned)pitch;  // pitch % 4 == 0: both rows share the byte phase
+    tp.u0 = lds_u32(q0); tp.u1 = lds_u32(q0 + 4); tp.u2 = lds_u32(q0 + 8);
+    tp.v0 = lds_u32(q1); tp.v1 = lds_u32(q1 + 4); tp.v2 = lds_u32(q1 + 8);
+    tp.h0 = (uint32_t)a0 << 3;
+    return tp;
+}
+__device__ __forceinline__ uint32_t crop_tile_finish(const CropTaps &tp)
+{
+    const uint32_t lo0 = __funnelshift_r(tp.u0, tp.u1, tp.h0), hi0 = __funnelshift_r(tp.u1, tp.u2, tp.h0);
+    const uint32_t lo1 = __funnelshift_r(tp.v0, tp.v1, tp.h0), hi1 = __funnelshift_r(tp.v1, tp.v2, tp.h0);
+    const uint32_t c_r = __byte_perm(lo0, lo1, 0x7430);  // [r00 r01 r10 r11]
+    const uint32_t c_t = __byte_perm(lo0, hi0, 0x5241);  // [g00 g01 b00 b01]
+    const uint32_t c_b = __byte_perm(lo1, hi1, 0x5241);  // [g10 g11 b10 b11]
+    const uint32_t fx = tp.fxy & 0xffffu, fy = tp.fxy >> 16;
+    const uint32_t wxp = fx * 0xffffu + 32u;             // (32 - fx) | fx << 16
+    const uint32_t W0 = (32u - fy) * wxp, W1 = fy * wxp; // (wy*wx0 | wy*wx1 << 16), each <= 1024
+    const uint32_t Sr = __dp2a_hi(W1, c_r, __dp2a_lo(W0, c_r, 512u));
+    const uint32_t Sg = __dp2a_lo(W1, c_b, __dp2a_lo(W0, c_t, 512u));
+    const uint32_t Sb = __dp2a_hi(W1, c_b, __dp2a_hi(W0, c_t, 512u));
+    return __byte_perm(__byte_perm(Sr << 6, Sg << 6, 0x4462), Sb << 6, 0x4610);
+}
+
+// Can the footprints of this person's tiles be fetched by TMA (warp_affine_u8_tma_kernel below)?
+// Tiles are 32 columns x tr rows (tr = 32, 16 or 8: the tallest whose box fits half the buffer, so
+// two boxes can be in flight).  The box is the same for every tile of the person -- a bound on
+// the footprint of any tile.  The Q10 column deltas are rint(m00*x*1024) (products exact in
+// float64) and the row bases rint((m01*y+m02)*1024)+16, both monotonic, so over a tile
+//   span(X) <= |m00|*31*1024 + |m01|*(tr-1)*1024 + 2 (+ 2^-20 from the one rounded addition)
+// and the tap columns number (Xmax>>10) + 2 - (Xmin>>10) <= (span >> 10) + 3; rows likewise.
+constexpr int CT_BOX = CT_SMEM / 2;  // one of the two TMA boxes
+struct CropPlan {
+    int lead, boxw, boxh, tr;
+    bool tma;
+};
+__device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw, int ss, const float *m)
+{
+    CropPlan p;
+    p.lead = (int)((uintptr_t)src & 15);
+    p.boxw = p.boxh = p.tr = 0;
+    p.tma = false;
+    const double a00 = fabs((double)m[0]) * 1024.0, a01 = fabs((double)m[1]) * 1024.0;
+    const double a10 = fabs((double)m[3]) * 1024.0, a11 = fabs((double)m[4]) * 1024.0;
+    // (also NaN) tame coefficients only: Q10 coordinates stay far from int32 overflow, boxes below 256
+    if (!(a00 < 8192.0 && a01 < 8192.0 && a10 < 8192.0 && a11 < 8192.0 && fabsf(m[2]) < 1048576.0f && fabsf(m[5]) < 1048576.0f))
+        return p;
+    if (!(sh > 0 && sw > 0 && ss >= 16 && (ss & 15) == 0)) return p;
+#pragma unroll
+    for (int tr = CT; tr >= 8; tr >>= 1) {
+        const int ex = (int)(a00 * 31.0 + a01 * (double)(tr - 1)), ey = (int)(a10 * 31.0 + a11 * (double)(tr - 1));
+        const int boxw = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
+        const int boxh = ((ey + 4) >> 10) + 3;
+        if (boxw <= 256 && boxh <= 256 && boxw * boxh <= CT_BOX) {
+            p.boxw = boxw; p.boxh = boxh; p.tr = tr; p.tma = true;
+            break;
+        }
+    }
+    return p;
+}
+
 __device__ __forceinline__ int q10_col(double m, int x) { return __double2int_rn(__dmul_rn(__dmul_rn(m, (double)x), 1024.0)); }
 __device__ __forceinline__ int q10_row(double m, double c, int y)
 {
@@ -227,7 +300,7 @@ __device__ __forceinline__ int q10_row(double m, double c, int y)
 // only on the person and the column (matrix, Q10 column deltas, image geometry) is computed once.
 __global__ void __launch_bounds__(CT_THREADS)
 warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
-                           const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H)
+                           const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H, int skip_tma)
 {
     extern __shared__ __align__(16) unsigned char fp[];  // footprint copy
     const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
@@ -243,6 +316,7 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
 
     const uint8_t *src = src_ptrs[n];
     const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
+    if (skip_tma && crop_plan(src, sh, sw, ss, m).tma) return;  // the TMA kernel does this person
     const int ssm = ss & 15;
     // the image buffer as 16-byte chunks: [buf, buf + lim + 16) may be read (images are < 2 GiB)
     const char *buf = reinterpret_cast<const char *>((uintptr_t)src & ~(uintptr_t)15);
@@ -370,7 +444,220 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Third generation: the footprint of a tile arrives with ONE TMA tensor load.
+//
+// The image is described to the TMA unit as a 2-D uint8 tensor (3*sw + lead bytes x sh rows, row
+// pitch = stride) based at the 16-byte-aligned address below the first pixel; the box is the
+// person's footprint bound (crop_plan).  Box coordinates are arbitrary byte / row positions,
+// positions (the byte start rounded down to 16: the TMA unit faults on anything else), and
+// whatever falls outside the tensor is filled with zeros by the hardware -- OpenCV's
+// constant-0 border with no bounds logic at all.  One CTA = one person: it patches a template
+// descriptor in shared memory (tensormap.replace: address, extents, pitch, box), publishes it
+// to a slot of a device-global ring (tensormap.cp_fenceproxy) and walks its tiles: thread 0
+// issues the load, everybody waits on the mbarrier, gathers (same integer pixel code as the
+// cp.async kernel, uniform phase 0) and meets at one barrier per tile.
+// Needs stride % 16 == 0 and a box that fits; other persons are left to the cp.async kernel.
+// ---------------------------------------------------------------------------------------
+constexpr int TM_SLOTS = 8192;  // ring of descriptors: a slot is rewritten 8192 CTAs later (<= 1184 CTAs are resident)
+__device__ __align__(128) unsigned char g_tmap_ring[TM_SLOTS][128];
+__device__ unsigned int g_tmap_next;
+
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "UDP_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra UDP_MBAR_DONE;\n"
+        "bra UDP_MBAR_WAIT;\n"
+        "UDP_MBAR_DONE:\n"
+        "}\n" ::"r"(mbar), "r"(parity) : "memory");
+}
+
+// ROWS rows (every fourth of a tile) of one warp: the taps of row i+1 are loaded before the
+// arithmetic, shuffles and store of row i.
+template <int ROWS>
+__device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bdx, int pitch, int K0, int p0, uint32_t osel,
+                                                 int lane, uint8_t *&outp, size_t out_step)
+{
+    int2 q[ROWS];
+#pragma unroll
+    for (int i = 0; i < ROWS; ++i) q[i] = rq[4 * i];
+    CropTaps cur = crop_tile_load(q[0].x + adx, q[0].y + bdx, pitch, K0);
+#pragma unroll
+    for (int i = 0; i < ROWS; ++i, outp += out_step) {
+        CropTaps nxt;
+        if (i + 1 < ROWS) nxt = crop_tile_load(q[i + 1].x + adx, q[i + 1].y + bdx, pitch, K0);
+        const uint32_t px = crop_tile_finish(cur);
+        const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1);
+        if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);
+        if (i + 1 < ROWS) cur = nxt;
+    }
+}
+
+__global__ void __launch_bounds__(CT_THREADS)
+warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_t *const *src_ptrs,
+                          const int32_t *src_h, const int32_t *src_w, const int32_t *src_stride,
+                          const float *M, uint8_t *dst, int W, int H)
+{
+    // 2 boxes of CT_BOX bytes | 128 B descriptor | 2 mbarriers | int4 colc[W/32] | int2 rowq[H]
+    extern __shared__ __align__(128) unsigned char fp[];
+    const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
+    const unsigned sdesc = fpa + CT_SMEM, mbar = sdesc + 128;
+    const int tiles_x = W / CT;
+    int4 *colc = reinterpret_cast<int4 *>(fp + CT_SMEM + 144);  // per tile column: min/max of the Q10 column deltas
+    int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + 144 + 16 * tiles_x);
+
+    const int n = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const float *m = M + 6 * (size_t)n;
+    const uint8_t *src = src_ptrs[n];
+    const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
+    const CropPlan pl = crop_plan(src, sh, sw, ss, m);
+    if (!pl.tma) return;
+    const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
+    const int lead = pl.lead, pitch = pl.boxw, TR = pl.tr;
+
+    for (int y = t; y < H; y += CT_THREADS) rowq[y] = make_int2(q10_row(m01, m02, y), q10_row(m11, m12, y));
+    for (int c = t; c < tiles_x; c += CT_THREADS) {
+        const int A0 = q10_col(m00, c * CT), A1 = q10_col(m00, c * CT + CT - 1);
+        const int B0 = q10_col(m10, c * CT), B1 = q10_col(m10, c * CT + CT - 1);
+        colc[c] = make_int4(min(A0, A1), max(A0, A1), min(B0, B1), max(B0, B1));
+    }
+    unsigned long long gdesc = 0;
+    if (warp == 0) {
+        reinterpret_cast<uint32_t *>(fp + CT_SMEM)[lane] = reinterpret_cast<const uint32_t *>(&tmpl)[lane];
+        __syncwarp();
+        unsigned slot = 0;
+        if (lane == 0) {
+            const unsigned long long base = (unsigned long long)(uintptr_t)src - (unsigned)lead;
+            asm volatile("tensormap.replace.tile.global_address.shared::cta.b1024.b64 [%0], %1;" ::"r"(sdesc), "l"(base) : "memory");
+            asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(3 * sw + lead) : "memory");
+            asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(sh) : "memory");
+            asm volatile("tensormap.replace.tile.global_stride.shared::cta.b1024.b64 [%0], 0, %1;" ::"r"(sdesc), "l"((unsigned long long)ss) : "memory");
+            asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pl.boxw) : "memory");
+            asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(pl.boxh) : "memory");
+            slot = atomicAdd(&g_tmap_next, 1u) & (TM_SLOTS - 1);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar + 8) : "memory");
+        }
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        gdesc = (unsigned long long)(uintptr_t)g_tmap_ring[slot];
+        asm volatile("tensormap.cp_fenceproxy.global.shared::cta.tensormap::generic.release.gpu.sync.aligned [%0], [%1], 128;"
+                     ::"l"(gdesc), "r"(sdesc) : "memory");
+        if (lane == 0) {
+            asm volatile("fence.proxy.tensormap::generic.acquire.gpu [%0], 128;" ::"l"(gdesc) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    __syncthreads();
+
+    int p0 = min((4 * lane) / 3, 30);
+    uint32_t osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
+    asm volatile("" : "+r"(p0), "+r"(osel));
+    const size_t row_bytes = (size_t)W * 3;
+    const size_t out_step = (size_t)(CT_THREADS / 32) * row_bytes;
+    const unsigned tx_bytes = (unsigned)(pl.boxw * pl.boxh);
+    const int ntiles = tiles_x * (H / TR);
+
+    // tile (cx, y0): first tap column / row of its footprint; the box starts at the 16-byte boundary below
+    auto corner = [&](int cx, int y0) {
+        const int2 qa = rowq[y0], qb = rowq[y0 + TR - 1];
+        const int4 cc = colc[cx];
+        return make_int2((min(qa.x, qb.x) + cc.x) >> 10, (min(qa.y, qb.y) + cc.z) >> 10);
+    };
+    auto issue = [&](int2 g, int b) {  // thread 0: arm the barrier of buffer b and start the load
+        const unsigned bar = mbar + 8 * b;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tx_bytes) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                     ::"r"(fpa + b * CT_BOX), "l"(gdesc), "r"((3 * g.x + lead) & ~15), "r"(g.y), "r"(bar) : "memory");
+    };
+
+    int2 nx = corner(0, 0);
+    if (t == 0) issue(nx, 0);
+    int cx = 0, y0 = 0, adx = 0, bdx = 0;
+    uint8_t *outp = dst;
+    for (int k = 0; k < ntiles; ++k) {
+        const int2 g = nx;
+        const int b = k & 1;
+        int ncx = cx, ny0 = y0 + TR;
+        if (ny0 >= H) { ny0 = 0; ++ncx; }
+        if (k + 1 < ntiles) {  // the other box was released by the barrier that ended tile k-1
+            nx = corner(ncx, ny0);
+            if (t == 0) issue(nx, b ^ 1);
+        }
+        if (y0 == 0) {  // new tile column: this lane's Q10 column deltas, output pointer
+            adx = q10_col(m00, cx * CT + lane);
+            bdx = q10_col(m10, cx * CT + lane);
+            outp = dst + ((size_t)n * H + warp) * row_bytes + (size_t)cx * (CT * 3) + 4 * lane;
+        }
+        const int xb = 3 * g.x + lead, c0 = xb & ~15, shift0 = xb & 15;
+        const unsigned box = fpa + b * CT_BOX;
+        mbar_wait(mbar + 8 * b, (k >> 1) & 1);
+        const bool fix = lead != 0 && c0 <= 0;  // bytes [0, lead) of a row precede the image: not zero-filled
+        if (fix) {
+            for (int rr = t; rr < pl.boxh; rr += CT_THREADS)
+                if ((unsigned)(g.y + rr) < (unsigned)sh) zero_bytes(fp + b * CT_BOX + rr * pitch, min(pitch, -c0), min(pitch, lead - c0));
+            __syncthreads();
+        }
+        const int K0 = (int)box + shift0 - g.y * pitch - 3 * g.x;
+        if (TR == CT) crop_gather_rows<CT / 4>(rowq + y0 + warp, adx, bdx, pitch, K0, p0, osel, lane, outp, out_step);
+        else if (TR == CT / 2) crop_gather_rows<CT / 8>(rowq + y0 + warp, adx, bdx, pitch, K0, p0, osel, lane, outp, out_step);
+        else crop_gather_rows<CT / 16>(rowq + y0 + warp, adx, bdx, pitch, K0, p0, osel, lane, outp, out_step);
+        if (fix) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes before the next TMA write
+        __syncthreads();  // this box may be refilled
+        cx = ncx; y0 = ny0;
+    }
+}
+
 }  // namespace udp
+
+// The template descriptor: any valid 2-D uint8 tiled map; every field that matters is replaced on
+// the device.  cuTensorMapEncodeTiled comes from the driver through the runtime (no -lcuda).
+static int crop_tma_template(CUtensorMap *out)
+{
+    static CUtensorMap tm;
+    static int state = 0;  // 1 ready, -1 unavailable
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    if (state == 0) {
+        state = -1;
+        typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                      const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void *fn = nullptr, *ring = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && fn &&
+            q == cudaDriverEntryPointSuccess && cudaGetSymbolAddress(&ring, udp::g_tmap_ring) == cudaSuccess) {
+            const cuuint64_t gdim[2] = {4096, 4096}, gstride[1] = {4096};
+            const cuuint32_t box[2] = {64, 32}, estride[2] = {1, 1};
+            if (((encode_fn)fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ring, gdim, gstride, box, estride,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
+                state = 1;
+        }
+        (void)cudaGetLastError();
+    }
+    if (state == 1) *out = tm;
+    return state;
+}
+
+static bool crop_tiles_ok(int W, int H)
+{
+    return !udp_force_generic() && W % udp::CT == 0 && H % udp::CT == 0 && H <= 1024 && W <= 2048;
+}
+static bool crop_tma_armed(CUtensorMap *tmpl)
+{
+    const char *no_tma = getenv("UDP_CROP_NO_TMA");
+    return !(no_tma && no_tma[0] == '1') && crop_tma_template(tmpl) == 1;
+}
+
+extern "C" int udp_warp_affine_launches(int W, int H)
+{
+    CUtensorMap tmpl;
+    return crop_tiles_ok(W, H) && crop_tma_armed(&tmpl) ? 2 : 1;
+}
 
 extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h,
                                   const int32_t *src_w, const int32_t *src_stride, const float *M,
@@ -379,13 +666,20 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
     if (N < 0 || W < 1 || H < 1 || (W & 1)) return UDP_EINVAL;
     if (N == 0) return 0;
     if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst) return UDP_EINVAL;
-    if (!udp_force_generic() && W % udp::CT == 0 && H % udp::CT == 0 && H <= 1024 && ((uintptr_t)dst & 3) == 0) {
+    if (crop_tiles_ok(W, H) && ((uintptr_t)dst & 3) == 0) {
         const int tiles_x = W / udp::CT;
+        CUtensorMap tmpl;
+        const int tma = crop_tma_armed(&tmpl);
+        if (tma) {  // persons whose images / boxes suit the TMA unit; the launch below does the others
+            udp::warp_affine_u8_tma_kernel<<<N, udp::CT_THREADS, udp::CT_SMEM + 144 + 16 * tiles_x + 8 * H, (cudaStream_t)stream>>>(
+                tmpl, src_ptrs, src_h, src_w, src_stride, M, dst, W, H);
+            UDP_LAUNCH_CHECK();
+        }
         for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
             const int nn = N - n0 < 65535 ? N - n0 : 65535;
             udp::warp_affine_u8_tile_kernel<<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, (cudaStream_t)stream>>>(
                 src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
-                dst + (size_t)n0 * H * W * 3, W, H);
+                dst + (size_t)n0 * H * W * 3, W, H, tma);
             UDP_LAUNCH_CHECK();
         }
         return 0;

@@ -110,6 +110,11 @@ def crop_batch(src, M, image_size, out=None):
     return out
 
 
+def crop_launches(image_size):
+    """Kernel launches one crop_batch() makes for this crop size (TMA kernel + cp.async kernel, or one)."""
+    return int(_lib.load().udp_warp_affine_launches(int(image_size[0]), int(image_size[1])))
+
+
 def rotate_points_batch(joints, rot_deg, center, scale, image_size, do_clip=False, out=None):
     """a3 rotate_points on joints [N,K,>=2] float64 -> float64 [N,K,2] (or into `out`
     [N,K,>=2], whose columns 0,1 are written)."""

@@ -119,7 +119,7 @@ class HostPipeline:
                     _, tw = D.encode_batch(cfg, j3, sl["vis"][:m], out=sl["target"][:m])
                 r = D.decode_batch(cfg, sl["out"][:m], sl["fl"][:m], sl["center"][:m], sl["scale"][:m],
                                    want_packed=True)
-                self.launches += 5
+                self.launches += 4 + D.crop_launches(cfg.image_size)
                 sl["ran"].record()
             with torch.cuda.stream(self.s_down):
                 self.s_down.wait_event(sl["ran"])
