@@ -280,7 +280,8 @@ __device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw
 #pragma unroll
     for (int tr = CT; tr >= 8; tr >>= 1) {
         const int ex = (int)(a00 * 31.0 + a01 * (double)(tr - 1)), ey = (int)(a10 * 31.0 + a11 * (double)(tr - 1));
-        const int boxw = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
+        int boxw = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
+        if (!(boxw & 16) && boxw < 256) boxw += 16;  // odd number of 16-byte chunks per row: rotated gathers spread over the banks
         const int boxh = ((ey + 4) >> 10) + 3;
         if (boxw <= 256 && boxh <= 256 && boxw * boxh <= CT_BOX) {
             p.boxw = boxw; p.boxh = boxh; p.tr = tr; p.tma = true;
