@@ -56,6 +56,18 @@ int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h, con
                        int N, void *stream);
 int udp_warp_affine_launches(int W, int H);
 
+/* a2 + SURVEY 8(f)-1: the crop with `transforms.ToTensor()` + `transforms.Normalize(mean, std)` fused
+ *     (deep_hrnet/tools/train.py:127-143, applied at JointsDataset.py:237-238), and the mirrored
+ *     network input of the flip test, `np.flip(input, 3)` (lib/core/function.py:154-155), as an
+ *     optional second output.  dst, dst_flipped [N,3,H,W] float32 = ((u8 / 255) - mean[c]) / std[c],
+ *     every step rounded as torch rounds it (bit-exact with torchvision on the bit-exact crop);
+ *     the uint8 crop is never written.  mean, std: HOST float[3].  dst_flipped may be NULL.
+ *     W and H must be multiples of 32 (every reference config), else UDP_EINVAL. */
+int udp_warp_affine_normalize_f32(const uint8_t *const *src_ptrs, const int32_t *src_h,
+                                  const int32_t *src_w, const int32_t *src_stride, const float *M,
+                                  const float *mean, const float *std_, float *dst, float *dst_flipped,
+                                  int W, int H, int N, void *stream);
+
 /* a3  rotate_points(joints[:, 0:2], r, c, image_size, s, do_clip)  JointsDataset.py:51-73, call :228.
  *     joints [N,K,jstride] float64 (x,y at 0,1), out [N,K,ostride] float64; may alias. */
 int udp_rotate_points(const double *joints, int jstride, const double *rot_deg, const void *center,

@@ -63,6 +63,23 @@ def rotate_points(joints_xy, rot_deg, center, scale, W, H, do_clip=False):
     return out
 
 
+def to_tensor_normalize(crop, mean, std):
+    """`transforms.Compose([ToTensor(), Normalize(mean, std)])` on the uint8 HWC crop
+    (deep_hrnet/tools/train.py:127-143, applied at JointsDataset.py:237-238).  The transforms live
+    in torchvision (pinned 0.9.1 by deep_hrnet/requirements.txt, not vendored in the reference):
+    ToTensor = HWC uint8 -> CHW float32 `.div(255)`; Normalize = `.sub_(mean).div_(std)` with
+    mean/std as float32 tensors.  Every step is one IEEE float32 operation, restated here in numpy
+    float32; pinned by tests/golden/normalize.npz (generated with torchvision itself)."""
+    x = np.ascontiguousarray(crop, np.uint8).astype(np.float32) / np.float32(255)
+    x = (x - np.asarray(mean, np.float32)) / np.asarray(std, np.float32)
+    return np.ascontiguousarray(x.transpose(2, 0, 1))
+
+
+def flip_input(x):
+    """The mirrored network input of the flip test: np.flip(input, 3) (core/function.py:154)."""
+    return np.ascontiguousarray(x[..., ::-1])
+
+
 def warp_affine_u8(src, M, W, H):
     """a2: src uint8 [Hs,Ws,3], M float32 [2,3] -> uint8 [H,W,3] (cv2.warpAffine,
     WARP_INVERSE_MAP|INTER_LINEAR, constant-0 border; JointsDataset.py:227)."""

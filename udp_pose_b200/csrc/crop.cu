@@ -15,6 +15,8 @@
 // once per CTA into shared memory; the per-pixel work is integer only.  The finished
 // ROWS x W x 3 byte tile is staged in shared memory and leaves as 16-byte streaming stores.
 #include <cuda.h>  // CUtensorMap and its enums (types only: the encoder is fetched with cudaGetDriverEntryPoint)
+#include <cmath>
+#include <cstring>
 #include <mutex>
 
 #include "decode_pipe.cuh"
@@ -297,11 +299,117 @@ __device__ __forceinline__ int q10_row(double m, double c, int y)
     return __double2int_rn(__dmul_rn(__dadd_rn(__dmul_rn(m, (double)y), c), 1024.0)) + 16;
 }
 
+// ---------------------------------------------------------------------------------------
+// Where a finished row of 32 pixels goes.  Both tiled kernels are templated on one of these:
+//   CropOutU8  -- the crop itself: uint8 HWC (a2), a warp's 96 bytes repacked into 24 word stores;
+//   CropOutF32 -- SURVEY 8(f) rank 1: ToTensor + Normalize fused into the crop
+//                 (tools/train.py:127-143, JointsDataset.py:237-238): float32 CHW
+//                 ((x / 255) - mean) / std, plus (optionally) the x-mirrored copy that the flip
+//                 test feeds the model (np.flip(input, 3), core/function.py:154-155).  Three
+//                 (six) fully coalesced 128-byte stores per warp row; the uint8 crop never
+//                 exists in memory.
+// Each lane owns one pixel of the row; a warp's next row is 4 below (CT_THREADS / 32).
+// ---------------------------------------------------------------------------------------
+struct CropU8Args {
+    uint8_t *dst;
+};
+struct CropOutU8 {
+    using Args = CropU8Args;
+    uint8_t *base, *p;
+    size_t row_bytes, step;
+    int p0;
+    uint32_t osel;
+    bool act;
+    __device__ __forceinline__ void init(const Args &a, int n, int W, int H, int lane)
+    {
+        // per-lane constants of the 96-byte row repack: word `lane` holds bytes 4*lane .. 4*lane+3
+        p0 = min((4 * lane) / 3, 30);
+        osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
+        asm volatile("" : "+r"(p0), "+r"(osel));  // keep them in registers (ptxas rematerialised them per pixel)
+        row_bytes = (size_t)W * 3;
+        step = (size_t)(CT_THREADS / 32) * row_bytes;
+        base = a.dst + (size_t)n * H * row_bytes + 4 * lane;
+        p = base;
+        act = lane < 24;
+    }
+    __device__ __forceinline__ void seek(int y, int x0) { p = base + (size_t)y * row_bytes + (size_t)x0 * 3; }
+    __device__ __forceinline__ void emit(uint32_t px)
+    {
+        const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1);
+        if (act) *reinterpret_cast<uint32_t *>(p) = __byte_perm(PA, PB, osel);
+        p += step;
+    }
+};
+
+struct CropF32Args {
+    float *dst, *dst_flipped;  // [N,3,H,W]; dst_flipped may be null
+    float mean[3], sd[3], inv[3];
+    int exact_div;             // 1: the reciprocal + one correction was checked on the host for all 256 inputs
+};
+// ((x / 255) - mean) / sd in float32, each step rounded as torch does (true divisions).
+__device__ __forceinline__ float crop_norm(uint32_t px, int c, float mean, float sd, float inv, bool fast)
+{
+    const float x = __fsub_rn(__uint_as_float(__byte_perm(px, 0x4B000000u, 0x7440u | (uint32_t)c)), 8388608.0f);  // byte c, exact
+    const float y = 0x1.010102p-8f;
+    const float q0 = __fmul_rn(x, y);
+    const float q = fmaf(fmaf(-q0, 255.0f, x), y, q0);  // x / 255 correctly rounded (div255; x >= 0)
+    const float t = __fsub_rn(q, mean);
+    if (!fast) return __fdiv_rn(t, sd);
+    const float u = __fmul_rn(t, inv);
+    return fmaf(fmaf(-u, sd, t), inv, u);
+}
+struct CropOutF32 {
+    using Args = CropF32Args;
+    float *base, *basef, *p, *pf;
+    size_t plane, step;
+    int W_;
+    float mean[3], sd[3], inv[3];
+    bool fast;
+    __device__ __forceinline__ void init(const Args &a, int n, int W, int H, int lane)
+    {
+        plane = (size_t)H * W;
+        step = (size_t)(CT_THREADS / 32) * W;
+        W_ = W;
+        base = a.dst + (size_t)n * 3 * plane + lane;
+        basef = a.dst_flipped ? a.dst_flipped + (size_t)n * 3 * plane + (W - 1 - lane) : nullptr;
+        p = base;
+        pf = basef;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { mean[c] = a.mean[c]; sd[c] = a.sd[c]; inv[c] = a.inv[c]; }
+        fast = a.exact_div != 0;
+    }
+    __device__ __forceinline__ void seek(int y, int x0)
+    {
+        p = base + (size_t)y * W_ + x0;
+        if (basef) pf = basef + (size_t)y * W_ - x0;
+    }
+    __device__ __forceinline__ void emit(uint32_t px)
+    {
+        const float v0 = crop_norm(px, 0, mean[0], sd[0], inv[0], fast);
+        const float v1 = crop_norm(px, 1, mean[1], sd[1], inv[1], fast);
+        const float v2 = crop_norm(px, 2, mean[2], sd[2], inv[2], fast);
+        __stcs(p, v0); __stcs(p + plane, v1); __stcs(p + 2 * plane, v2);
+        p += step;
+        if (basef) {
+            __stcs(pf, v0); __stcs(pf + plane, v1); __stcs(pf + 2 * plane, v2);
+            pf += step;
+        }
+    }
+};
+
+__host__ __device__ inline void crop_args_advance(CropU8Args &a, size_t elems) { a.dst += elems; }
+__host__ __device__ inline void crop_args_advance(CropF32Args &a, size_t elems)
+{
+    a.dst += elems;
+    if (a.dst_flipped) a.dst_flipped += elems;
+}
+
 // grid = (tile columns, persons); a CTA walks down its tile column, so everything that depends
 // only on the person and the column (matrix, Q10 column deltas, image geometry) is computed once.
+template <class OUT>
 __global__ void __launch_bounds__(CT_THREADS)
 warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
-                           const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H, int skip_tma)
+                           const int32_t *src_stride, const float *M, typename OUT::Args oargs, int W, int H, int skip_tma)
 {
     extern __shared__ __align__(16) unsigned char fp[];  // footprint copy
     const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
@@ -324,12 +432,8 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
     const int lead = (int)((uintptr_t)src & 15);
     const bool img_ok = sh > 0 && sw > 0;
     const unsigned lim = img_ok ? (unsigned)((((long long)(sh - 1) * ss + 3LL * sw + lead + 15) & ~15LL) - 16) : 0u;
-    // per-lane constants of the 96-byte row repack: word `lane` holds bytes 4*lane .. 4*lane+3
-    int p0 = min((4 * lane) / 3, 30);
-    uint32_t osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
-    asm volatile("" : "+r"(p0), "+r"(osel));  // keep them in registers (ptxas rematerialised them per pixel)
-    const size_t row_bytes = (size_t)W * 3;
-    uint8_t *out_tile = dst + ((size_t)n * H + warp) * row_bytes + (size_t)x0 * 3 + 4 * lane;  // + y0 rows below
+    OUT out;
+    out.init(oargs, n, W, H, lane);
 
     // Q10 row bases of the whole tile column, once per CTA (float64 products, as OpenCV rounds them)
     int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + 16);
@@ -346,7 +450,7 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
         return g;
     };
 
-    for (int y0 = 0; y0 < H; y0 += CT, out_tile += CT * row_bytes) {
+    for (int y0 = 0; y0 < H; y0 += CT) {
         auto bbox_rows = [&](int ry0, int rows) { return bbox(rowq[y0 + ry0], rowq[y0 + ry0 + rows - 1]); };
         TileGeom g = bbox_rows(0, CT);
         // rows per pass: the whole tile unless its footprint does not fit the buffer (large scale)
@@ -419,16 +523,13 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
                 }
             }
             const int K0 = (int)fpa + shift0 - g.ya * pitch - 3 * g.xa;
-            uint8_t *outp = out_tile + (size_t)ry0 * row_bytes;
-            const size_t out_step = (size_t)(CT_THREADS / 32) * row_bytes;
+            out.seek(y0 + ry0 + warp, x0);
             // rows of this pass owned by this warp: ry0 + warp + 4*i; their Q10 bases come from rowq
 #define UDP_CROP_ROWS(PIXEL_EXPR)                                                                     \
-            for (int r = ry0 + warp; r < ry0 + nr; r += CT_THREADS / 32, outp += out_step) {         \
+            for (int r = ry0 + warp; r < ry0 + nr; r += CT_THREADS / 32) {                            \
                 const int2 q = rowq[y0 + r];                                                          \
                 const int X = q.x + adx, Y = q.y + bdx;                                               \
-                const uint32_t px = (PIXEL_EXPR);                                                     \
-                const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1); \
-                if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);       \
+                out.emit(PIXEL_EXPR);                                                                 \
             }
             if (direct) {  // absurd scale: per-pixel global path
                 UDP_CROP_ROWS(crop_border_pixel(src, sh, sw, ss, X, Y))
@@ -479,29 +580,27 @@ __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
 
 // ROWS rows (every fourth of a tile) of one warp: the taps of row i+1 are loaded before the
 // arithmetic, shuffles and store of row i.
-template <int ROWS>
-__device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bdx, int pitch, int K0, int p0, uint32_t osel,
-                                                 int lane, uint8_t *&outp, size_t out_step)
+template <int ROWS, class OUT>
+__device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bdx, int pitch, int K0, OUT &out)
 {
     int2 q[ROWS];
 #pragma unroll
     for (int i = 0; i < ROWS; ++i) q[i] = rq[4 * i];
     CropTaps cur = crop_tile_load(q[0].x + adx, q[0].y + bdx, pitch, K0);
 #pragma unroll
-    for (int i = 0; i < ROWS; ++i, outp += out_step) {
+    for (int i = 0; i < ROWS; ++i) {
         CropTaps nxt;
         if (i + 1 < ROWS) nxt = crop_tile_load(q[i + 1].x + adx, q[i + 1].y + bdx, pitch, K0);
-        const uint32_t px = crop_tile_finish(cur);
-        const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1);
-        if (lane < 24) *reinterpret_cast<uint32_t *>(outp) = __byte_perm(PA, PB, osel);
+        out.emit(crop_tile_finish(cur));
         if (i + 1 < ROWS) cur = nxt;
     }
 }
 
+template <class OUT>
 __global__ void __launch_bounds__(CT_THREADS)
 warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_t *const *src_ptrs,
                           const int32_t *src_h, const int32_t *src_w, const int32_t *src_stride,
-                          const float *M, uint8_t *dst, int W, int H)
+                          const float *M, typename OUT::Args oargs, int W, int H)
 {
     // 2 boxes of CT_BOX bytes | 128 B descriptor | 2 mbarriers | int4 colc[W/32] | int2 rowq[H]
     extern __shared__ __align__(128) unsigned char fp[];
@@ -554,11 +653,8 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
     }
     __syncthreads();
 
-    int p0 = min((4 * lane) / 3, 30);
-    uint32_t osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
-    asm volatile("" : "+r"(p0), "+r"(osel));
-    const size_t row_bytes = (size_t)W * 3;
-    const size_t out_step = (size_t)(CT_THREADS / 32) * row_bytes;
+    OUT out;
+    out.init(oargs, n, W, H, lane);
     const unsigned tx_bytes = (unsigned)(pl.boxw * pl.boxh);
     const int ntiles = tiles_x * (H / TR);
 
@@ -578,7 +674,6 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
     int2 nx = corner(0, 0);
     if (t == 0) issue(nx, 0);
     int cx = 0, y0 = 0, adx = 0, bdx = 0;
-    uint8_t *outp = dst;
     for (int k = 0; k < ntiles; ++k) {
         const int2 g = nx;
         const int b = k & 1;
@@ -591,7 +686,7 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
         if (y0 == 0) {  // new tile column: this lane's Q10 column deltas, output pointer
             adx = q10_col(m00, cx * CT + lane);
             bdx = q10_col(m10, cx * CT + lane);
-            outp = dst + ((size_t)n * H + warp) * row_bytes + (size_t)cx * (CT * 3) + 4 * lane;
+            out.seek(warp, cx * CT);
         }
         const int xb = 3 * g.x + lead, c0 = xb & ~15, shift0 = xb & 15;
         const unsigned box = fpa + b * CT_BOX;
@@ -603,9 +698,9 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
             __syncthreads();
         }
         const int K0 = (int)box + shift0 - g.y * pitch - 3 * g.x;
-        if (TR == CT) crop_gather_rows<CT / 4>(rowq + y0 + warp, adx, bdx, pitch, K0, p0, osel, lane, outp, out_step);
-        else if (TR == CT / 2) crop_gather_rows<CT / 8>(rowq + y0 + warp, adx, bdx, pitch, K0, p0, osel, lane, outp, out_step);
-        else crop_gather_rows<CT / 16>(rowq + y0 + warp, adx, bdx, pitch, K0, p0, osel, lane, outp, out_step);
+        if (TR == CT) crop_gather_rows<CT / 4>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
+        else if (TR == CT / 2) crop_gather_rows<CT / 8>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
+        else crop_gather_rows<CT / 16>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
         if (fix) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes before the next TMA write
         __syncthreads();  // this box may be refilled
         cx = ncx; y0 = ny0;
@@ -660,6 +755,30 @@ extern "C" int udp_warp_affine_launches(int W, int H)
     return crop_tiles_ok(W, H) && crop_tma_armed(&tmpl) ? 2 : 1;
 }
 
+template <class OUT>
+static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
+                             const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
+                             size_t person_elems, int W, int H, int N, cudaStream_t stream)
+{
+    const int tiles_x = W / udp::CT;
+    CUtensorMap tmpl;
+    const int tma = crop_tma_armed(&tmpl);
+    if (tma) {  // persons whose images / boxes suit the TMA unit; the launch below does the others
+        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 144 + 16 * tiles_x + 8 * H, stream>>>(
+            tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
+        UDP_LAUNCH_CHECK();
+    }
+    for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
+        const int nn = N - n0 < 65535 ? N - n0 : 65535;
+        typename OUT::Args a = oargs;
+        udp::crop_args_advance(a, (size_t)n0 * person_elems);
+        udp::warp_affine_u8_tile_kernel<OUT><<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, stream>>>(
+            src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0, a, W, H, tma);
+        UDP_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
 extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h,
                                   const int32_t *src_w, const int32_t *src_stride, const float *M,
                                   uint8_t *dst, int W, int H, int N, void *stream)
@@ -668,22 +787,9 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
     if (N == 0) return 0;
     if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst) return UDP_EINVAL;
     if (crop_tiles_ok(W, H) && ((uintptr_t)dst & 3) == 0) {
-        const int tiles_x = W / udp::CT;
-        CUtensorMap tmpl;
-        const int tma = crop_tma_armed(&tmpl);
-        if (tma) {  // persons whose images / boxes suit the TMA unit; the launch below does the others
-            udp::warp_affine_u8_tma_kernel<<<N, udp::CT_THREADS, udp::CT_SMEM + 144 + 16 * tiles_x + 8 * H, (cudaStream_t)stream>>>(
-                tmpl, src_ptrs, src_h, src_w, src_stride, M, dst, W, H);
-            UDP_LAUNCH_CHECK();
-        }
-        for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
-            const int nn = N - n0 < 65535 ? N - n0 : 65535;
-            udp::warp_affine_u8_tile_kernel<<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, (cudaStream_t)stream>>>(
-                src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0,
-                dst + (size_t)n0 * H * W * 3, W, H, tma);
-            UDP_LAUNCH_CHECK();
-        }
-        return 0;
+        udp::CropU8Args a{dst};
+        return crop_launch_tiled<udp::CropOutU8>(src_ptrs, src_h, src_w, src_stride, M, a, (size_t)H * W * 3, W, H, N,
+                                                 (cudaStream_t)stream);
     }
     size_t smem = sizeof(int32_t) * (2 * (size_t)W + 2 * udp::CROP_ROWS) + (size_t)udp::CROP_ROWS * W * 3;
     if (smem > 200 * 1024) return UDP_EINVAL;
@@ -702,4 +808,46 @@ extern "C" int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t 
         UDP_LAUNCH_CHECK();
     }
     return 0;
+}
+
+// float32 x / y for the 256 inputs of one channel: does reciprocal + one FMA correction give
+// the correctly rounded quotient everywhere?  (It does for the ImageNet constants; any other
+// constants are checked here, on the host, and fall back to a true division if not.)
+static bool crop_norm_fast_ok(const float mean[3], const float sd[3], float inv[3])
+{
+    bool ok = true;
+    for (int c = 0; c < 3; ++c) {
+        inv[c] = 1.0f / sd[c];
+        for (int b = 0; b < 256 && ok; ++b) {
+            const float t = (float)b / 255.0f - mean[c];
+            const float u = t * inv[c];
+            const float q = std::fmaf(std::fmaf(-u, sd[c], t), inv[c], u);
+            const float want = t / sd[c];
+            ok = std::memcmp(&q, &want, 4) == 0;
+        }
+    }
+    return ok;
+}
+
+extern "C" int udp_warp_affine_normalize_f32(const uint8_t *const *src_ptrs, const int32_t *src_h,
+                                             const int32_t *src_w, const int32_t *src_stride, const float *M,
+                                             const float *mean, const float *std_, float *dst, float *dst_flipped,
+                                             int W, int H, int N, void *stream)
+{
+    if (N < 0 || W < 1 || H < 1 || !mean || !std_) return UDP_EINVAL;
+    if (!crop_tiles_ok(W, H)) return UDP_EINVAL;  // crop sizes in multiples of 32 (every reference config)
+    if (N == 0) return 0;
+    if (!src_ptrs || !src_h || !src_w || !src_stride || !M || !dst || dst == dst_flipped) return UDP_EINVAL;
+    if ((((uintptr_t)dst | (uintptr_t)dst_flipped) & 3) != 0) return UDP_EINVAL;
+    udp::CropF32Args a;
+    a.dst = dst;
+    a.dst_flipped = dst_flipped;
+    for (int c = 0; c < 3; ++c) {
+        if (!(std_[c] != 0.0f)) return UDP_EINVAL;
+        a.mean[c] = mean[c];
+        a.sd[c] = std_[c];
+    }
+    a.exact_div = crop_norm_fast_ok(a.mean, a.sd, a.inv) ? 1 : 0;
+    return crop_launch_tiled<udp::CropOutF32>(src_ptrs, src_h, src_w, src_stride, M, a, (size_t)3 * H * W, W, H, N,
+                                              (cudaStream_t)stream);
 }

@@ -110,6 +110,30 @@ def crop_batch(src, M, image_size, out=None):
     return out
 
 
+IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)  # tools/train.py:127-129
+
+
+def crop_normalize_batch(src, M, image_size, mean=IMAGENET_MEAN, std=IMAGENET_STD, want_flipped=False,
+                         out=None, out_flipped=None):
+    """a2 with ToTensor + Normalize fused (tools/train.py:127-143,
+    JointsDataset.py:237-238) -> float32 [N,3,H,W]; with want_flipped also np.flip(input, 3)
+    (core/function.py:154) -- the two network inputs of the flip test from one gather."""
+    W, H = int(image_size[0]), int(image_size[1])
+    M = _dev(M, _F32)
+    N = M.shape[0]
+    assert src.n == N
+    if out is None:
+        out = torch.empty((N, 3, H, W), dtype=_F32, device=M.device)
+    if want_flipped and out_flipped is None:
+        out_flipped = torch.empty((N, 3, H, W), dtype=_F32, device=M.device)
+    mean_c = (C.c_float * 3)(*[float(v) for v in mean])
+    std_c = (C.c_float * 3)(*[float(v) for v in std])
+    _lib.call("udp_warp_affine_normalize_f32", _ptr(src.ptrs), _ptr(src.h), _ptr(src.w), _ptr(src.stride),
+              _ptr(M), C.cast(mean_c, C.c_void_p), C.cast(std_c, C.c_void_p), _ptr(out),
+              _ptr(out_flipped) if want_flipped else None, W, H, N, _stream())
+    return (out, out_flipped) if want_flipped else out
+
+
 def crop_launches(image_size):
     """Kernel launches one crop_batch() makes for this crop size (TMA kernel + cp.async kernel, or one)."""
     return int(_lib.load().udp_warp_affine_launches(int(image_size[0]), int(image_size[1])))
