@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fused", action="store_true", help="skip the 8(f)-1 fused crop+normalize timing")
     ap.add_argument("--config", type=int, default=CFG_ID)
     ap.add_argument("--images", type=int, default=N_IMAGES, help="source image pool (SURVEY 8d: 64; 256 exceeds L2)")
     return ap.parse_args()
@@ -429,6 +430,29 @@ def run_ours(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     total_ms = float(tt[0])
 
+    # ---- SURVEY 8(f)-1 (outside the timed step): crop + ToTensor + Normalize + mirrored input, one gather
+    fused = None
+    if world == 1 and not args.no_fused:
+        M = D.warp_matrices(wl["center"], wl["scale"], wl["rot"], cfg.image_size)
+        fo = torch.empty((B, 3, H, W), dtype=torch.float32, device="cuda")
+        ff = torch.empty_like(fo)
+        fused = {}
+        for key, flip in (("crop_normalize", False), ("crop_normalize_flip", True)):
+            for _ in range(3):
+                D.crop_normalize_batch(src, M, cfg.image_size, want_flipped=flip, out=fo, out_flipped=ff if flip else None)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = max(5, min(args.steps, 20))
+            a.record()
+            for _ in range(reps):
+                D.crop_normalize_batch(src, M, cfg.image_size, want_flipped=flip, out=fo, out_flipped=ff if flip else None)
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b) / reps
+            bpp = 3.0 * wl["src_area"] + 24 + 12.0 * W * H * (2 if flip else 1)
+            fused[key] = {"ms": round(ms, 4), "bytes_per_person": round(bpp, 1)}
+        del fo, ff
+        torch.cuda.empty_cache()
+
     # ---- end to end through host buffers (pinned), H2D and D2H inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -516,6 +540,12 @@ def run_ours(args):
             "gather_ms": round(stage_ms["gather"], 4),
             "gpu_launches": (len(STAGES) - 1 + D.crop_launches(cfg.image_size)) * args.steps,
             "clocks": clocks}
+    if fused:
+        for v in fused.values():
+            v["achieved_gbs"] = round(v["bytes_per_person"] * B / (v["ms"] * 1e-3) / 1e9, 1)
+            v["frac"] = round(v["achieved_gbs"] / peak, 4)
+        line["next"] = dict(fused, note="SURVEY 8(f)-1, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
+                                        "as float32 CHW (and the x-mirrored flip-test input) straight from the gather; not part of `value`")
     if e2e:
         line["e2e"] = e2e
     if not args.no_cpu and world == 1:

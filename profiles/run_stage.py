@@ -26,6 +26,9 @@ for _ in range(a.iters):
     if "crop" in st:
         M = D.warp_matrices(wl["center"], wl["scale"], wl["rot"], cfg.image_size)
         D.crop_batch(src, M, cfg.image_size)
+    if "fused" in st:  # crop + ToTensor + Normalize + mirrored input
+        M = D.warp_matrices(wl["center"], wl["scale"], wl["rot"], cfg.image_size)
+        D.crop_normalize_batch(src, M, cfg.image_size, want_flipped=True)
     if "encode" in st:
         j3 = D.rotate_points_batch(wl["joints"], wl["rot"], wl["center"], wl["scale"], cfg.image_size)
         D.encode_batch(cfg, j3, wl["vis"])

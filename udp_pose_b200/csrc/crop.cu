@@ -262,7 +262,11 @@ __device__ __forceinline__ uint32_t crop_tile_finish(const CropTaps &tp)
 // float64) and the row bases rint((m01*y+m02)*1024)+16, both monotonic, so over a tile
 //   span(X) <= |m00|*31*1024 + |m01|*(tr-1)*1024 + 2 (+ 2^-20 from the one rounded addition)
 // and the tap columns number (Xmax>>10) + 2 - (Xmin>>10) <= (span >> 10) + 3; rows likewise.
-constexpr int CT_BOX = CT_SMEM / 2;  // one of the two TMA boxes
+#ifndef UDP_CROP_NBOX
+#define UDP_CROP_NBOX 2
+#endif
+constexpr int CT_NBOX = UDP_CROP_NBOX;                   // TMA boxes in flight per CTA
+constexpr int CT_BOX = (CT_SMEM / CT_NBOX) & ~127;  // one box
 struct CropPlan {
     int lead, boxw, boxh, tr;
     bool tma;
@@ -310,11 +314,15 @@ __device__ __forceinline__ int q10_row(double m, double c, int y)
 //                 exists in memory.
 // Each lane owns one pixel of the row; a warp's next row is 4 below (CT_THREADS / 32).
 // ---------------------------------------------------------------------------------------
+#ifndef UDP_CROP_U8_ROWMAJOR
+#define UDP_CROP_U8_ROWMAJOR false
+#endif
 struct CropU8Args {
     uint8_t *dst;
 };
 struct CropOutU8 {
     using Args = CropU8Args;
+    static constexpr bool ROW_MAJOR = UDP_CROP_U8_ROWMAJOR;
     uint8_t *base, *p;
     size_t row_bytes, step;
     int p0;
@@ -360,10 +368,12 @@ __device__ __forceinline__ float crop_norm(uint32_t px, int c, float mean, float
 }
 struct CropOutF32 {
     using Args = CropF32Args;
+    static constexpr bool ROW_MAJOR = false;
     float *base, *basef, *p, *pf;
     size_t plane, step;
     int W_;
-    float mean[3], sd[3], inv[3];
+    f32x2 nmean01, nsd01, inv01;  // channels 0 and 1 ride the packed FP32 pipe
+    float mean2, sd2, inv2;
     bool fast;
     __device__ __forceinline__ void init(const Args &a, int n, int W, int H, int lane)
     {
@@ -374,8 +384,10 @@ struct CropOutF32 {
         basef = a.dst_flipped ? a.dst_flipped + (size_t)n * 3 * plane + (W - 1 - lane) : nullptr;
         p = base;
         pf = basef;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { mean[c] = a.mean[c]; sd[c] = a.sd[c]; inv[c] = a.inv[c]; }
+        nmean01 = pk(-a.mean[0], -a.mean[1]);
+        nsd01 = pk(-a.sd[0], -a.sd[1]);
+        inv01 = pk(a.inv[0], a.inv[1]);
+        mean2 = a.mean[2]; sd2 = a.sd[2]; inv2 = a.inv[2];
         fast = a.exact_div != 0;
     }
     __device__ __forceinline__ void seek(int y, int x0)
@@ -385,9 +397,23 @@ struct CropOutF32 {
     }
     __device__ __forceinline__ void emit(uint32_t px)
     {
-        const float v0 = crop_norm(px, 0, mean[0], sd[0], inv[0], fast);
-        const float v1 = crop_norm(px, 1, mean[1], sd[1], inv[1], fast);
-        const float v2 = crop_norm(px, 2, mean[2], sd[2], inv[2], fast);
+        float v0, v1;
+        const float v2 = crop_norm(px, 2, mean2, sd2, inv2, fast);
+        if (fast) {  // the same operations as crop_norm, two channels per instruction
+            const float y = 0x1.010102p-8f;
+            const f32x2 x = fsub2p(pk(__uint_as_float(__byte_perm(px, 0x4B000000u, 0x7440u)),
+                                      __uint_as_float(__byte_perm(px, 0x4B000000u, 0x7441u))), pk(8388608.0f, 8388608.0f));
+            const f32x2 q0 = fmul2p(x, y);
+            const f32x2 q = ffma2p(ffma2p(q0, -255.0f, x), y, q0);
+            const f32x2 t = fadd2p(q, nmean01);
+            const f32x2 u = fmul2pp(t, inv01);
+            const f32x2 o = ffma2pp(ffma2pp(u, nsd01, t), inv01, u);
+            v0 = lo_of(o);
+            v1 = hi_of(o);
+        } else {
+            v0 = crop_norm(px, 0, -lo_of(nmean01), -lo_of(nsd01), lo_of(inv01), false);
+            v1 = crop_norm(px, 1, -hi_of(nmean01), -hi_of(nsd01), hi_of(inv01), false);
+        }
         __stcs(p, v0); __stcs(p + plane, v1); __stcs(p + 2 * plane, v2);
         p += step;
         if (basef) {
@@ -602,13 +628,13 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
                           const int32_t *src_h, const int32_t *src_w, const int32_t *src_stride,
                           const float *M, typename OUT::Args oargs, int W, int H)
 {
-    // 2 boxes of CT_BOX bytes | 128 B descriptor | 2 mbarriers | int4 colc[W/32] | int2 rowq[H]
+    // CT_NBOX boxes of CT_BOX bytes | 128 B descriptor | 32 B of mbarriers | int4 colc[W/32] | int2 rowq[H]
     extern __shared__ __align__(128) unsigned char fp[];
     const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
     const unsigned sdesc = fpa + CT_SMEM, mbar = sdesc + 128;
     const int tiles_x = W / CT;
-    int4 *colc = reinterpret_cast<int4 *>(fp + CT_SMEM + 144);  // per tile column: min/max of the Q10 column deltas
-    int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + 144 + 16 * tiles_x);
+    int4 *colc = reinterpret_cast<int4 *>(fp + CT_SMEM + 160);  // per tile column: min/max of the Q10 column deltas
+    int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + 160 + 16 * tiles_x);
 
     const int n = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const float *m = M + 6 * (size_t)n;
@@ -639,8 +665,8 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
             asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pl.boxw) : "memory");
             asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(pl.boxh) : "memory");
             slot = atomicAdd(&g_tmap_next, 1u) & (TM_SLOTS - 1);
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar) : "memory");
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar + 8) : "memory");
+#pragma unroll
+            for (int i = 0; i < CT_NBOX; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar + 8 * i) : "memory");
         }
         slot = __shfl_sync(0xffffffffu, slot, 0);
         gdesc = (unsigned long long)(uintptr_t)g_tmap_ring[slot];
@@ -671,26 +697,46 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
                      ::"r"(fpa + b * CT_BOX), "l"(gdesc), "r"((3 * g.x + lead) & ~15), "r"(g.y), "r"(bar) : "memory");
     };
 
-    int2 nx = corner(0, 0);
-    if (t == 0) issue(nx, 0);
-    int cx = 0, y0 = 0, adx = 0, bdx = 0;
-    for (int k = 0; k < ntiles; ++k) {
-        const int2 g = nx;
-        const int b = k & 1;
-        int ncx = cx, ny0 = y0 + TR;
-        if (ny0 >= H) { ny0 = 0; ++ncx; }
-        if (k + 1 < ntiles) {  // the other box was released by the barrier that ended tile k-1
-            nx = corner(ncx, ny0);
-            if (t == 0) issue(nx, b ^ 1);
+    // tile order: down a tile column, then the next column (ROW_MAJOR: across first).  The load
+    // cursor runs CT_NBOX - 1 tiles ahead of the gather cursor; tile k lives in box k % CT_NBOX.
+    auto advance = [&](int &cx_, int &y0_) {
+        if (OUT::ROW_MAJOR) {
+            if (++cx_ == tiles_x) { cx_ = 0; y0_ += TR; }
+        } else {
+            y0_ += TR;
+            if (y0_ >= H) { y0_ = 0; ++cx_; }
         }
-        if (y0 == 0) {  // new tile column: this lane's Q10 column deltas, output pointer
+    };
+    int2 gq[CT_NBOX];  // corners of the tiles in flight (gq[0] = the tile being gathered)
+    int lcx = 0, ly0 = 0, lbox = 0;  // load cursor
+#pragma unroll
+    for (int i = 0; i < CT_NBOX - 1; ++i) {
+        gq[i] = make_int2(0, 0);
+        if (i < ntiles) {
+            gq[i] = corner(lcx, ly0);
+            if (t == 0) issue(gq[i], lbox);
+            advance(lcx, ly0);
+            lbox = lbox + 1 == CT_NBOX ? 0 : lbox + 1;
+        }
+    }
+    int cx = 0, y0 = 0, adx = 0, bdx = 0, b = 0;
+    unsigned par = 0;  // parity of box b's current fill
+    for (int k = 0; k < ntiles; ++k) {
+        const int2 g = gq[0];
+        if (k + CT_NBOX - 1 < ntiles) {  // the box being refilled was released by the barrier that ended tile k-1
+            gq[CT_NBOX - 1] = corner(lcx, ly0);
+            if (t == 0) issue(gq[CT_NBOX - 1], lbox);
+            advance(lcx, ly0);
+            lbox = lbox + 1 == CT_NBOX ? 0 : lbox + 1;
+        }
+        if (OUT::ROW_MAJOR || y0 == 0) {  // new tile column: this lane's Q10 column deltas, output pointer
             adx = q10_col(m00, cx * CT + lane);
             bdx = q10_col(m10, cx * CT + lane);
-            out.seek(warp, cx * CT);
+            out.seek(y0 + warp, cx * CT);
         }
         const int xb = 3 * g.x + lead, c0 = xb & ~15, shift0 = xb & 15;
         const unsigned box = fpa + b * CT_BOX;
-        mbar_wait(mbar + 8 * b, (k >> 1) & 1);
+        mbar_wait(mbar + 8 * b, par);
         const bool fix = lead != 0 && c0 <= 0;  // bytes [0, lead) of a row precede the image: not zero-filled
         if (fix) {
             for (int rr = t; rr < pl.boxh; rr += CT_THREADS)
@@ -703,7 +749,10 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
         else crop_gather_rows<CT / 16>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
         if (fix) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes before the next TMA write
         __syncthreads();  // this box may be refilled
-        cx = ncx; y0 = ny0;
+        advance(cx, y0);
+#pragma unroll
+        for (int i = 0; i + 1 < CT_NBOX; ++i) gq[i] = gq[i + 1];
+        if (++b == CT_NBOX) { b = 0; par ^= 1u; }
     }
 }
 
@@ -764,7 +813,7 @@ static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_
     CUtensorMap tmpl;
     const int tma = crop_tma_armed(&tmpl);
     if (tma) {  // persons whose images / boxes suit the TMA unit; the launch below does the others
-        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 144 + 16 * tiles_x + 8 * H, stream>>>(
+        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 160 + 16 * tiles_x + 8 * H, stream>>>(
             tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
         UDP_LAUNCH_CHECK();
     }
