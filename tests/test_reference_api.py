@@ -141,3 +141,26 @@ def test_getitem_eval_and_train_rng_order(R):
     s = g["scale"][0] * np.clip(np.random.randn() * sf + 1, 1 - sf, 1 + sf)
     r = np.clip(np.random.randn() * rf, -rf * 2, rf * 2) if random.random() <= 0.6 else 0
     assert np.array_equal(meta["scale"], s) and meta["rotation"] == r
+
+
+def test_get_batch_with_fused_normalize(R):
+    """get_batch(normalize=(mean, std)) returns what the reference's DataLoader hands the model:
+    Normalize(ToTensor(crop)) float32 CHW (tools/train.py:127-143), plus np.flip(input, 3)
+    (core/function.py:154) -- bit-exact against the transform of the golden crops."""
+    import torch
+    from oracle import oracle as O
+    from udp_pose_b200 import device_api as D
+    cfg, g = CONFIGS[1], parity.load(1)
+    ds = _dataset(R, cfg)
+    n = len(g["src_index"])
+    ds.db = [dict(image="mem://%d" % i, joints_3d=g["joints_src"][i].copy(), joints_3d_vis=g["joints_vis"][i].copy(),
+                  center=g["center"][i].copy(), scale=g["scale"][i].copy(), score=0.5) for i in range(n)]
+    idx = [i for i in range(n) if g["rot"][i] == 0]
+    imgs = [g["src_images"][g["src_index"][i]] for i in idx]
+    (x, xf), t, tw, metas = ds.get_batch(idx, imgs, normalize=(D.IMAGENET_MEAN, D.IMAGENET_STD), want_flipped=True)
+    assert x.dtype == torch.float32 and tuple(x.shape[1:]) == (3, 256, 192)
+    assert torch.equal(xf, x.flip(3))
+    xh = x.cpu().numpy()
+    for k, i in enumerate(idx):
+        want = O.to_tensor_normalize(g["crop"][i], D.IMAGENET_MEAN, D.IMAGENET_STD)
+        assert np.array_equal(xh[k].view(np.uint32), want.view(np.uint32))

@@ -210,9 +210,13 @@ class JointsDataset(torch.utils.data.Dataset):
                 c[0] = img.shape[1] - c[0] - 1
         return img, joints, joints_vis, c, s, r
 
-    def get_batch(self, indices, images=None):
+    def get_batch(self, indices, images=None, normalize=None, want_flipped=False):
         """Batched __getitem__: returns (input uint8 CUDA [N,H,W,3], target CUDA, target_weight
-        CUDA, metas).  `images` (optional) supplies decoded uint8 arrays instead of files."""
+        CUDA, metas).  `images` (optional) supplies decoded uint8 arrays instead of files.
+        normalize=(mean, std): the reference's `transforms.Compose([ToTensor(), Normalize(mean, std)])`
+        (tools/train.py:127-143) is fused into the crop and `input` is float32 CUDA [N,3,H,W]
+        (SURVEY 8f-1); with want_flipped it is the pair (input, np.flip(input, 3)) that the flip
+        test feeds the model (core/function.py:154-155)."""
         W, H = int(self.image_size[0]), int(self.image_size[1])
         recs, imgs, js, vs, cs, ss, rs = [], [], [], [], [], [], []
         for n, idx in enumerate(indices):
@@ -224,7 +228,11 @@ class JointsDataset(torch.utils.data.Dataset):
         c, s = _csN(np.stack(cs), np.stack(ss))
         rot = np.asarray(rs, np.float64)
         M = D.warp_matrices(c, s, rot, (W, H))
-        inp = D.crop_batch(D.SourceImages(imgs, np.arange(len(imgs))), M, (W, H))
+        src = D.SourceImages(imgs, np.arange(len(imgs)))
+        if normalize is not None:
+            inp = D.crop_normalize_batch(src, M, (W, H), normalize[0], normalize[1], want_flipped=want_flipped)
+        else:
+            inp = D.crop_batch(src, M, (W, H))
         j = np.ascontiguousarray(np.stack(js), np.float64)
         jd = torch.from_numpy(j).cuda()
         D.rotate_points_batch(jd, rot, c, s, (W, H), do_clip=False, out=jd)
