@@ -287,9 +287,9 @@ __device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw
     for (int tr = CT; tr >= 8; tr >>= 1) {
         const int ex = (int)(a00 * 31.0 + a01 * (double)(tr - 1)), ey = (int)(a10 * 31.0 + a11 * (double)(tr - 1));
         int boxw = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
-        if (!(boxw & 16) && boxw < 256) boxw += 16;  // odd number of 16-byte chunks per row: rotated gathers spread over the banks
+        if (!(boxw & 16) && boxw < 512) boxw += 16;  // odd number of 16-byte chunks per row: rotated gathers spread over the banks
         const int boxh = ((ey + 4) >> 10) + 3;
-        if (boxw <= 256 && boxh <= 256 && boxw * boxh <= CT_BOX) {
+        if (boxw <= 512 && boxh <= 256 && boxw * boxh <= CT_BOX) {  // 256 two-byte elements per box row at most
             p.boxw = boxw; p.boxh = boxh; p.tr = tr; p.tma = true;
             break;
         }
@@ -575,8 +575,9 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
 // ---------------------------------------------------------------------------------------
 // Third generation: the footprint of a tile arrives with ONE TMA tensor load.
 //
-// The image is described to the TMA unit as a 2-D uint8 tensor (3*sw + lead bytes x sh rows, row
-// pitch = stride) based at the 16-byte-aligned address below the first pixel; the box is the
+// The image is described to the TMA unit as a 2-D tensor of two-byte elements (a box row may then be
+// 512 bytes: scales up to 5 source pixels per output pixel) of 3*sw + lead bytes x sh rows, row
+// pitch = stride, based at the 16-byte-aligned address below the first pixel; the box is the
 // person's footprint bound (crop_plan).  Box coordinates are arbitrary byte / row positions,
 // positions (the byte start rounded down to 16: the TMA unit faults on anything else), and
 // whatever falls outside the tensor is filled with zeros by the hardware -- OpenCV's
@@ -659,10 +660,10 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
         if (lane == 0) {
             const unsigned long long base = (unsigned long long)(uintptr_t)src - (unsigned)lead;
             asm volatile("tensormap.replace.tile.global_address.shared::cta.b1024.b64 [%0], %1;" ::"r"(sdesc), "l"(base) : "memory");
-            asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(3 * sw + lead) : "memory");
+            asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"((3 * sw + lead + 1) >> 1) : "memory");
             asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(sh) : "memory");
             asm volatile("tensormap.replace.tile.global_stride.shared::cta.b1024.b64 [%0], 0, %1;" ::"r"(sdesc), "l"((unsigned long long)ss) : "memory");
-            asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pl.boxw) : "memory");
+            asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pl.boxw >> 1) : "memory");
             asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(pl.boxh) : "memory");
             slot = atomicAdd(&g_tmap_next, 1u) & (TM_SLOTS - 1);
 #pragma unroll
@@ -694,7 +695,7 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
         const unsigned bar = mbar + 8 * b;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tx_bytes) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                     ::"r"(fpa + b * CT_BOX), "l"(gdesc), "r"((3 * g.x + lead) & ~15), "r"(g.y), "r"(bar) : "memory");
+                     ::"r"(fpa + b * CT_BOX), "l"(gdesc), "r"(((3 * g.x + lead) & ~15) >> 1), "r"(g.y), "r"(bar) : "memory");
     };
 
     // tile order: down a tile column, then the next column (ROW_MAJOR: across first).  The load
@@ -737,10 +738,17 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
         const int xb = 3 * g.x + lead, c0 = xb & ~15, shift0 = xb & 15;
         const unsigned box = fpa + b * CT_BOX;
         mbar_wait(mbar + 8 * b, par);
-        const bool fix = lead != 0 && c0 <= 0;  // bytes [0, lead) of a row precede the image: not zero-filled
+        // not zero-filled by the hardware: bytes [0, lead) of a row (they precede the image) and,
+        // when the row has an odd number of bytes, the second half of its last two-byte element
+        const int rowb = 3 * sw + lead;
+        const bool fix_l = lead != 0 && c0 <= 0, fix_r = (rowb & 1) && c0 <= rowb && rowb < c0 + pitch;
+        const bool fix = fix_l || fix_r;
         if (fix) {
             for (int rr = t; rr < pl.boxh; rr += CT_THREADS)
-                if ((unsigned)(g.y + rr) < (unsigned)sh) zero_bytes(fp + b * CT_BOX + rr * pitch, min(pitch, -c0), min(pitch, lead - c0));
+                if ((unsigned)(g.y + rr) < (unsigned)sh) {
+                    if (fix_l) zero_bytes(fp + b * CT_BOX + rr * pitch, min(pitch, -c0), min(pitch, lead - c0));
+                    if (fix_r) fp[b * CT_BOX + rr * pitch + (rowb - c0)] = 0;
+                }
             __syncthreads();
         }
         const int K0 = (int)box + shift0 - g.y * pitch - 3 * g.x;
@@ -777,7 +785,7 @@ static int crop_tma_template(CUtensorMap *out)
             q == cudaDriverEntryPointSuccess && cudaGetSymbolAddress(&ring, udp::g_tmap_ring) == cudaSuccess) {
             const cuuint64_t gdim[2] = {4096, 4096}, gstride[1] = {4096};
             const cuuint32_t box[2] = {64, 32}, estride[2] = {1, 1};
-            if (((encode_fn)fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ring, gdim, gstride, box, estride,
+            if (((encode_fn)fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, ring, gdim, gstride, box, estride,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
                 state = 1;
