@@ -452,6 +452,17 @@ def run_ours(args):
             fused[key] = {"ms": round(ms, 4), "bytes_per_person": round(bpp, 1)}
         del fo, ff
         torch.cuda.empty_cache()
+        if cfg.target_type != "rsn":  # accuracy()/PCK of the network output against the target
+            cs = 3 if cfg.target_type == "offset" else 1
+            for _ in range(3):
+                D.accuracy_pck(wl["out"], target, cs)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                D.accuracy_pck(wl["out"], target, cs)
+            b.record()
+            torch.cuda.synchronize()
+            fused["accuracy_pck"] = {"ms": round(a.elapsed_time(b) / reps, 4), "bytes_per_person": 2.0 * K * h * w * 4 + 8 * K + 8 * K}
 
     # ---- end to end through host buffers (pinned), H2D and D2H inside the timed region
     e2e = None
@@ -544,8 +555,9 @@ def run_ours(args):
         for v in fused.values():
             v["achieved_gbs"] = round(v["bytes_per_person"] * B / (v["ms"] * 1e-3) / 1e9, 1)
             v["frac"] = round(v["achieved_gbs"] / peak, 4)
-        line["next"] = dict(fused, note="SURVEY 8(f)-1, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
-                                        "as float32 CHW (and the x-mirrored flip-test input) straight from the gather; not part of `value`")
+        line["next"] = dict(fused, note="SURVEY 8(f) ranks 1-2, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
+                                        "as float32 CHW (and the x-mirrored flip-test input) straight from the gather; udp_accuracy_pck is evaluate.py:accuracy "
+                                        "on device tensors; not part of `value`")
     if e2e:
         line["e2e"] = e2e
     if not args.no_cpu and world == 1:

@@ -150,6 +150,16 @@ int udp_decode_offset(const float *out, const float *out_flipped, const int32_t 
                       int h, float *preds, float *maxvals, float *preds_in, int32_t *argmax_idx,
                       float *packed, int N, void *stream);
 
+/* SURVEY 8(f)-2  accuracy(output, target, hm_type='gaussian', thr)  deep_hrnet/lib/core/evaluate.py:16-71,
+ *     call sites lib/core/function.py:76-80 and :187-192 (offset mode passes the [:, ::3] views:
+ *     ch_stride = 3).  output, target [N, K*ch_stride, h, w] float32 (16-byte aligned, h*w % 4 == 0).
+ *     pred [N,K,2] float32 = get_max_preds(output) coordinates (the 4th return value);
+ *     dists [K,N] float64 scratch/out (calc_dists, -1 = ignored); acc [K+1] float64 (acc[0] = average,
+ *     acc[1+j] = joint j or -1), avg_acc [1] float64, cnt [1] int32 -- all DEVICE pointers.  K <= 32. */
+int udp_accuracy_pck(const float *output, const float *target, int ch_stride, int K, int w, int h,
+                     int N, double thr, float *pred, double *dists, double *acc, double *avg_acc,
+                     int32_t *cnt, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -63,6 +63,41 @@ def rotate_points(joints_xy, rot_deg, center, scale, W, H, do_clip=False):
     return out
 
 
+def accuracy_pck(output, target, thr=0.5):
+    """accuracy(output, target, 'gaussian', thr) of deep_hrnet/lib/core/evaluate.py:41-71
+    (calc_dists :16-28, dist_acc :31-38), restated with array operations in the same dtypes:
+    get_max_preds on both tensors (core/inference.py:30-58), float32 coords / float64 norm
+    (h, w)/10, float64 distances, -1 where the target peak is not > 1 in x and y.
+    Returns (acc [K+1] f64, avg_acc, cnt, pred f32 [N,K,2]).  Pinned by tests/golden/accuracy.npz
+    (outputs of the reference's own accuracy())."""
+    def max_preds(hm):
+        N, K, h, w = hm.shape
+        flat = hm.reshape(N, K, -1)
+        idx = np.argmax(flat, 2)
+        mv = np.take_along_axis(flat, idx[..., None], 2)[..., 0]
+        p = np.stack([idx % w, idx // w], -1).astype(np.float32)
+        return p * (mv > 0.0)[..., None].astype(np.float32)
+    output, target = np.asarray(output, np.float32), np.asarray(target, np.float32)
+    N, K, h, w = output.shape
+    pred, tgt = max_preds(output), max_preds(target)
+    norm = np.ones((N, 2)) * np.array([h, w]) / 10
+    d = pred / norm[:, None, :] - tgt / norm[:, None, :]
+    dist = np.sqrt(d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1])
+    dist = np.where((tgt[..., 0] > 1) & (tgt[..., 1] > 1), dist, -1.0).T  # [K, N]
+    acc = np.zeros(K + 1)
+    s, cnt = 0, 0
+    for j in range(K):
+        cal = dist[j] != -1
+        a = (dist[j][cal] < thr).sum() * 1.0 / cal.sum() if cal.sum() > 0 else -1
+        acc[j + 1] = a
+        if a >= 0:
+            s, cnt = s + a, cnt + 1
+    avg = s / cnt if cnt != 0 else 0
+    if cnt != 0:
+        acc[0] = avg
+    return acc, avg, cnt, pred
+
+
 def to_tensor_normalize(crop, mean, std):
     """`transforms.Compose([ToTensor(), Normalize(mean, std)])` on the uint8 HWC crop
     (deep_hrnet/tools/train.py:127-143, applied at JointsDataset.py:237-238).  The transforms live

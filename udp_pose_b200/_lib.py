@@ -17,6 +17,7 @@ SIGNATURES = {
     "udp_warp_matrices": [_vp, _vp, _i, _vp, _i, _i, _vp, _i, _vp],
     "udp_warp_affine_u8": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "udp_warp_affine_launches": [_i, _i],
+    "udp_accuracy_pck": [_vp, _vp, _i, _i, _i, _i, _i, C.c_double, _vp, _vp, _vp, _vp, _vp, _vp],
     "udp_warp_affine_normalize_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "udp_rotate_points": [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _i, _i, _i, _vp],
     "udp_rsn_transform_joints": [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp],

@@ -1,0 +1,136 @@
+// evaluate.cu -- SURVEY 8(f)-2: accuracy() / PCK on the device.
+//
+// Reference: deep_hrnet/lib/core/evaluate.py:16-71 (calc_dists, dist_acc, accuracy), called once
+// per batch from lib/core/function.py:76-80 (train) and :187-192 (validate) on
+// `output.cpu().numpy()` and `target.cpu().numpy()` -- the second per-batch device-to-host round
+// trip of validate().  accuracy() = two get_max_preds (core/inference.py:30-58: flat first-index
+// argmax, coordinates zeroed where maxval <= 0), a normalised distance per (joint, person) and a
+// thresholded count per joint.
+//
+// Kernel 1 (one CTA per (person, joint)): streams the output map and the target map once with
+//   16-byte loads, block-wide np.argmax-exact (value, first index) reductions, then
+//   dists[c][n] = || pred/norm - target/norm ||  (float64, norm = (h, w)/10 -- the reference
+//   divides x by h/10 and y by w/10, evaluate.py:55) or -1 when the target peak is not > 1 in both
+//   coordinates (:21).  HBM-bound: 2*h*w*4 bytes per (person, joint), read once.
+// Kernel 2 (one CTA, one warp per joint): dist_acc per joint (:31-38) and the average over the
+//   joints that have any valid distance (:60-70), float64, joint order as in the reference.
+#include "blur.cuh"
+
+namespace udp {
+
+constexpr int PCK_THREADS = 128;
+
+__device__ __forceinline__ void pck_scan(const float *__restrict__ map, int hw, float &bv, int &bi)
+{
+    bv = -INFINITY;
+    bi = 0x7fffffff;
+    const int n4 = hw >> 2;
+    for (int q0 = threadIdx.x; q0 < n4; q0 += 4 * PCK_THREADS) {  // four 16-byte loads in flight per thread
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int q = q0 + u * PCK_THREADS;
+            v[u] = q < n4 ? ld_stream_f4(map + 4 * q) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i0 = 4 * (q0 + u * PCK_THREADS);
+            if (q0 + u * PCK_THREADS < n4) {
+                if (arg_better(v[u].x, i0, bv, bi)) { bv = v[u].x; bi = i0; }
+                if (arg_better(v[u].y, i0 + 1, bv, bi)) { bv = v[u].y; bi = i0 + 1; }
+                if (arg_better(v[u].z, i0 + 2, bv, bi)) { bv = v[u].z; bi = i0 + 2; }
+                if (arg_better(v[u].w, i0 + 3, bv, bi)) { bv = v[u].w; bi = i0 + 3; }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(PCK_THREADS)
+pck_dist_kernel(const float *__restrict__ output, const float *__restrict__ target, int ch_stride, int K, int w,
+                int h, int N, float *__restrict__ pred, double *__restrict__ dists)
+{
+    __shared__ float red_v[32];
+    __shared__ int red_i[32];
+    const int hw = h * w;
+    const long long m = blockIdx.x;  // (person, joint)
+    const int n = (int)(m / K), c = (int)(m - (long long)n * K);
+    const long long off = ((long long)n * K * ch_stride + (long long)c * ch_stride) * hw;
+    float ov, tv;
+    int oi, ti;
+    pck_scan(output + off, hw, ov, oi);
+    pck_scan(target + off, hw, tv, ti);
+    block_argmax(ov, oi, red_v, red_i);
+    block_argmax(tv, ti, red_v, red_i);
+    if (threadIdx.x == 0) {
+        // get_max_preds: (idx % w, floor(idx / w)) * (maxval > 0)
+        const bool om = ov > 0.0f, tm = tv > 0.0f;
+        const float px = om ? (float)(oi % w) : 0.0f, py = om ? (float)(oi / w) : 0.0f;
+        const float tx = tm ? (float)(ti % w) : 0.0f, ty = tm ? (float)(ti / w) : 0.0f;
+        pred[2 * m] = px;
+        pred[2 * m + 1] = py;
+        double d = -1.0;
+        if (tx > 1.0f && ty > 1.0f) {
+            const double nx = __ddiv_rn((double)h, 10.0), ny = __ddiv_rn((double)w, 10.0);  // np.array([h, w]) / 10
+            const double dx = __dsub_rn(__ddiv_rn((double)px, nx), __ddiv_rn((double)tx, nx));
+            const double dy = __dsub_rn(__ddiv_rn((double)py, ny), __ddiv_rn((double)ty, ny));
+            d = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+        }
+        dists[(long long)c * N + n] = d;  // [K, N], as calc_dists lays it out
+    }
+}
+
+__global__ void pck_acc_kernel(const double *__restrict__ dists, int K, int N, double thr, double *__restrict__ acc,
+                               double *__restrict__ avg_acc, int *__restrict__ cnt_out)
+{
+    __shared__ double s_acc[32];
+    const int lane = threadIdx.x & 31, c = threadIdx.x >> 5;
+    if (c < K) {
+        int valid = 0, below = 0;
+        for (int n = lane; n < N; n += 32) {
+            const double d = dists[(long long)c * N + n];
+            valid += d != -1.0;
+            below += d != -1.0 && d < thr;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            valid += __shfl_xor_sync(0xffffffffu, valid, o);
+            below += __shfl_xor_sync(0xffffffffu, below, o);
+        }
+        if (lane == 0) s_acc[c] = valid > 0 ? __ddiv_rn(__dmul_rn((double)below, 1.0), (double)valid) : -1.0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double sum = 0.0;
+        int cnt = 0;
+        for (int j = 0; j < K; ++j) {
+            acc[j + 1] = s_acc[j];
+            if (s_acc[j] >= 0.0) { sum = __dadd_rn(sum, s_acc[j]); ++cnt; }
+        }
+        const double avg = cnt != 0 ? __ddiv_rn(sum, (double)cnt) : 0.0;
+        acc[0] = cnt != 0 ? avg : 0.0;
+        *avg_acc = avg;
+        *cnt_out = cnt;
+    }
+}
+
+}  // namespace udp
+
+extern "C" int udp_accuracy_pck(const float *output, const float *target, int ch_stride, int K, int w, int h,
+                                int N, double thr, float *pred, double *dists, double *acc, double *avg_acc,
+                                int32_t *cnt, void *stream)
+{
+    if (N < 0 || K < 1 || K > 32 || w < 1 || h < 1 || ch_stride < 1 || ((w * h) & 3)) return UDP_EINVAL;
+    if (!acc || !avg_acc || !cnt) return UDP_EINVAL;
+    if (N > 0 && (!output || !target || !pred || !dists)) return UDP_EINVAL;
+    if ((((uintptr_t)output | (uintptr_t)target) & 15) != 0) return UDP_EINVAL;  // 16-byte vector loads
+    const long long maps = (long long)N * K;
+    if (maps > 0x7fffffffLL) return UDP_EINVAL;
+    if (maps > 0) {
+        udp::pck_dist_kernel<<<(unsigned)maps, udp::PCK_THREADS, 0, (cudaStream_t)stream>>>(output, target, ch_stride, K, w, h, N,
+                                                                                           pred, dists);
+        UDP_LAUNCH_CHECK();
+    }
+    udp::pck_acc_kernel<<<1, 32 * K, 0, (cudaStream_t)stream>>>(dists, K, N, thr, acc, avg_acc, cnt);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}

@@ -338,3 +338,23 @@ def transform_preds_batch(coords, center, scale, heatmap_size):
     _lib.call("udp_transform_preds", _ptr(coords), int(coords.dtype == _F64), _ptr(center),
               _ptr(scale), f64, int(heatmap_size[0]), int(heatmap_size[1]), _ptr(out), K, N, _stream())
     return out
+
+
+def accuracy_pck(output, target, ch_stride=1, thr=0.5):
+    """accuracy() of lib/core/evaluate.py:41-71 on device tensors.
+    output, target float32 CUDA [N, K*ch_stride, h, w] (offset mode: ch_stride=3, the [:, ::3]
+    views of function.py:190-191).  Returns dict(acc f64 [K+1], avg_acc f64 [1], cnt i32 [1],
+    pred f32 [N,K,2], dists f64 [K,N]) -- CUDA tensors, nothing synchronised."""
+    output, target = _dev(output, _F32), _dev(target, _F32)
+    assert output.shape == target.shape and output.dim() == 4 and output.shape[1] % ch_stride == 0
+    N, C, h, w = output.shape
+    K = C // ch_stride
+    dev = output.device
+    pred = torch.empty((N, K, 2), dtype=_F32, device=dev)
+    dists = torch.empty((K, N), dtype=_F64, device=dev)
+    acc = torch.empty((K + 1,), dtype=_F64, device=dev)
+    avg = torch.empty((1,), dtype=_F64, device=dev)
+    cnt = torch.empty((1,), dtype=torch.int32, device=dev)
+    _lib.call("udp_accuracy_pck", _ptr(output), _ptr(target), int(ch_stride), K, int(w), int(h), N, float(thr),
+              _ptr(pred), _ptr(dists), _ptr(acc), _ptr(avg), _ptr(cnt), _stream())
+    return dict(acc=acc, avg_acc=avg, cnt=cnt, pred=pred, dists=dists)

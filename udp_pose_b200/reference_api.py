@@ -375,10 +375,24 @@ def rsn_get_results(outputs, center, scale, output_flipped=None, flip_pairs=None
 
 
 # --------------------------------------------------------------------------------- install
-def install(inference=None, transforms=None, joints_dataset=None):
+def accuracy(output, target, hm_type='gaussian', thr=0.5):
+    """lib/core/evaluate.py:41-71 -> (acc float64 [K+1], avg_acc, cnt, pred float32 [N,K,2]).
+    Accepts numpy arrays (as the reference) or CUDA tensors (skipping the .cpu().numpy() of
+    function.py:76-80,187-192); strided [:, ::3] views of the offset mode are gathered on the
+    device side.  Only hm_type='gaussian' defines `pred` in the reference (:51-55)."""
+    if hm_type != 'gaussian':
+        raise ValueError("accuracy(): the reference defines pred only for hm_type='gaussian' (evaluate.py:51-55)")
+    o = output if isinstance(output, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(output, np.float32))
+    t = target if isinstance(target, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(target, np.float32))
+    r = D.accuracy_pck(o.contiguous(), t.contiguous(), 1, thr)
+    acc = _np(r["acc"])
+    return acc, float(_np(r["avg_acc"])[0]) if int(_np(r["cnt"])[0]) else 0, int(_np(r["cnt"])[0]), _np(r["pred"])
+
+
+def install(inference=None, transforms=None, joints_dataset=None, evaluate=None):
     """Substitute the CUDA codec into already-imported reference modules
-    (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset).  Returns a dict
-    {(module_name, attr): original} so the caller can undo it."""
+    (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset, lib.core.evaluate).
+    Returns a dict {(module_name, attr): original} so the caller can undo it."""
     saved = {}
 
     def put(mod, name, fn):
@@ -391,6 +405,7 @@ def install(inference=None, transforms=None, joints_dataset=None):
         put(inference, nm, globals()[nm])
     for nm in ("flip_back", "flip_back_offset", "fliplr_joints", "transform_preds"):
         put(transforms, nm, globals()[nm])
+    put(evaluate, "accuracy", accuracy)
     if joints_dataset is not None:
         put(joints_dataset, "get_warpmatrix", get_warpmatrix)
         put(joints_dataset, "rotate_points", rotate_points)
