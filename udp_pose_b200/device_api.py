@@ -139,6 +139,19 @@ def crop_launches(image_size):
     return int(_lib.load().udp_warp_affine_launches(int(image_size[0]), int(image_size[1])))
 
 
+def _joints3(joints, vis):
+    """generate_target reads joints[:, 0:2] of a [K,3] array (JointsDataset.py:313-314): the C ABI takes
+    rows of 3 doubles.  [N,K,2] coordinates (rotate_points' own output) are widened here."""
+    joints, vis = _dev(joints, _F64), _dev(vis, _F64)
+    if joints.dim() != 3 or joints.shape[2] not in (2, 3):
+        raise ValueError("joints must be [N,K,2] or [N,K,3], got %s" % (tuple(joints.shape),))
+    if joints.shape[2] == 2:
+        joints = torch.cat([joints, torch.zeros_like(joints[..., :1])], 2).contiguous()
+    if tuple(vis.shape) != (joints.shape[0], joints.shape[1], 3):
+        raise ValueError("joints_vis must be [N,K,3], got %s" % (tuple(vis.shape),))
+    return joints, vis
+
+
 def rotate_points_batch(joints, rot_deg, center, scale, image_size, do_clip=False, out=None):
     """a3 rotate_points on joints [N,K,>=2] float64 -> float64 [N,K,2] (or into `out`
     [N,K,>=2], whose columns 0,1 are written)."""
@@ -188,7 +201,7 @@ def fliplr_joints_batch(joints, vis, width, pairs, mul_vis=True):
 # -------------------------------------------------------------------------- encode side
 def encode_gaussian(joints, vis, image_size, heatmap_size, sigma, joints_weight=None, out=None):
     """a5 -> (target f32 [N,K,h,w], target_weight f32 [N,K,1])."""
-    joints, vis = _dev(joints, _F64), _dev(vis, _F64)
+    joints, vis = _joints3(joints, vis)
     N, K, _ = joints.shape
     (W, H), (w, h) = image_size, heatmap_size
     tgt = out if out is not None else torch.empty((N, K, h, w), dtype=_F32, device=joints.device)
@@ -201,7 +214,7 @@ def encode_gaussian(joints, vis, image_size, heatmap_size, sigma, joints_weight=
 
 def encode_offset(joints, vis, image_size, heatmap_size, kpd, joints_weight=None, out=None):
     """a6 -> (target f32 [N,3K,h,w], target_weight f32 [N,K,1])."""
-    joints, vis = _dev(joints, _F64), _dev(vis, _F64)
+    joints, vis = _joints3(joints, vis)
     N, K, _ = joints.shape
     (W, H), (w, h) = image_size, heatmap_size
     tgt = out if out is not None else torch.empty((N, 3 * K, h, w), dtype=_F32, device=joints.device)

@@ -60,7 +60,7 @@ from .configs import RSN_SIGMAS as D_RSN  # noqa: E402
 class HostPipeline:
     """Chunked, stream-overlapped codec pass over a HostBatch."""
 
-    def __init__(self, cfg, chunk, n_images, src_hw=(480, 640), device="cuda"):
+    def __init__(self, cfg, chunk, n_images, src_hw=(480, 640), device="cuda", n_slots=3):
         self.cfg, self.chunk, self.dev = cfg, chunk, torch.device(device)
         K, C = cfg.num_joints, cfg.channels
         (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
@@ -84,18 +84,23 @@ class HostPipeline:
                 target=torch.empty((chunk, tc, h, w), dtype=torch.float32, device=dev),
                 up=torch.cuda.Event(), ran=torch.cuda.Event(), down=torch.cuda.Event(),
             )
-        self.slots = [slot(), slot()]
+        self.slots = [slot() for _ in range(max(2, n_slots))]
+        self.chunks_done = 0
         self.launches = 0
 
-    def run(self, hb):
+    def run(self, hb, sync=True):
         """One pass over the HostBatch `hb`; results land in hb.crop/target/target_weight/keypoints.
-        Returns after everything is back on the host."""
+        Returns after everything is back on the host; with sync=False it returns once everything is
+        enqueued (a following run() then overlaps its uploads with this one's downloads --
+        call synchronize() before reading the host buffers)."""
         cfg, n, chunk = self.cfg, hb.n, self.chunk
         with torch.cuda.stream(self.s_up):
+            self.s_up.wait_stream(self.s_run)  # kernels of an unsynchronised previous run still read the images
             self.images.copy_(hb.images, non_blocking=True)
-        for ci, lo in enumerate(range(0, n, chunk)):
+        for lo in range(0, n, chunk):
             m = min(chunk, n - lo)
-            sl = self.slots[ci & 1]
+            sl = self.slots[self.chunks_done % len(self.slots)]
+            self.chunks_done += 1
             sel = slice(lo, lo + m)
             with torch.cuda.stream(self.s_up):
                 self.s_up.wait_event(sl["down"])  # slot free again (previous download finished)
@@ -131,5 +136,9 @@ class HostPipeline:
                 # keep the temporaries alive until the download stream is done with them
                 tw.record_stream(self.s_down)
                 r["packed"].record_stream(self.s_down)
+        if sync:
+            self.synchronize()
+
+    def synchronize(self):
         self.s_down.synchronize()
         self.s_run.synchronize()
