@@ -64,7 +64,8 @@ def test_pipeline_matches_direct_calls(cid):
     got = (hb.crop, hb.target, hb.target_weight, hb.keypoints)
     for a, b in zip(want, got):
         assert torch.equal(a, b)
-    assert pipe.launches == 6 * (4 + 2)
+    assert pipe.launches == len(pipe._schedule(n)) * (4 + 2)
+    assert sum(m for _, m in pipe._schedule(2048)) == 2048 and pipe._schedule(2048)[0][1] == chunk // 4
     # two passes without a synchronisation in between (streaming callers), then one wait
     for t in got:
         t.fill_(0)

@@ -88,6 +88,31 @@ class HostPipeline:
         self.chunks_done = 0
         self.launches = 0
 
+    def _schedule(self, n):
+        """(offset, size) of the chunks of one pass.  The first upload has no download to overlap
+        and the last download no upload, so the pass ramps up and down through quarter and half
+        chunks: the exposed head and tail of the pipeline shrink fourfold."""
+        c = self.chunk
+        head = [s for s in (c // 4, c // 2) if s >= 16]
+        sizes, left = [], n
+        if n >= 2 * (sum(head) + c):
+            for s in head:
+                sizes.append(s)
+            left -= 2 * sum(head)
+            while left > 0:
+                sizes.append(min(c, left))
+                left -= sizes[-1]
+            sizes += head[::-1]
+        else:
+            while left > 0:
+                sizes.append(min(c, left))
+                left -= sizes[-1]
+        out, lo = [], 0
+        for s in sizes:
+            out.append((lo, s))
+            lo += s
+        return out
+
     def run(self, hb, sync=True):
         """One pass over the HostBatch `hb`; results land in hb.crop/target/target_weight/keypoints.
         Returns after everything is back on the host; with sync=False it returns once everything is
@@ -97,8 +122,7 @@ class HostPipeline:
         with torch.cuda.stream(self.s_up):
             self.s_up.wait_stream(self.s_run)  # kernels of an unsynchronised previous run still read the images
             self.images.copy_(hb.images, non_blocking=True)
-        for lo in range(0, n, chunk):
-            m = min(chunk, n - lo)
+        for lo, m in self._schedule(n):
             sl = self.slots[self.chunks_done % len(self.slots)]
             self.chunks_done += 1
             sel = slice(lo, lo + m)
