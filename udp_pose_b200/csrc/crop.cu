@@ -588,9 +588,14 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
 // cp.async kernel, uniform phase 0) and meets at one barrier per tile.
 // Needs stride % 16 == 0 and a box that fits; other persons are left to the cp.async kernel.
 // ---------------------------------------------------------------------------------------
-constexpr int TM_SLOTS = 8192;  // ring of descriptors: a slot is rewritten 8192 CTAs later (<= 1184 CTAs are resident)
+// Pool of descriptors in global memory (the library allocates nothing at run time).  A CTA claims
+// a free slot with one compare-and-swap, starting at a ticket so that claims rarely collide, and
+// releases it after its last load has landed; 8192 slots against at most a few thousand resident
+// CTAs (all streams together), so the first probe almost always succeeds.
+constexpr int TM_SLOTS = 8192;
 __device__ __align__(128) unsigned char g_tmap_ring[TM_SLOTS][128];
 __device__ unsigned int g_tmap_next;
+__device__ unsigned int g_tmap_busy[TM_SLOTS];
 
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
 {
@@ -666,6 +671,7 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
             asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pl.boxw >> 1) : "memory");
             asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(pl.boxh) : "memory");
             slot = atomicAdd(&g_tmap_next, 1u) & (TM_SLOTS - 1);
+            while (atomicCAS(&g_tmap_busy[slot], 0u, 1u) != 0u) slot = (slot + 1) & (TM_SLOTS - 1);
 #pragma unroll
             for (int i = 0; i < CT_NBOX; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar + 8 * i) : "memory");
         }
@@ -762,6 +768,8 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
         for (int i = 0; i + 1 < CT_NBOX; ++i) gq[i] = gq[i + 1];
         if (++b == CT_NBOX) { b = 0; par ^= 1u; }
     }
+    // every load of this CTA has landed (each tile waited on its barrier): hand the descriptor slot back
+    if (t == 0) atomicExch(&g_tmap_busy[(gdesc - (unsigned long long)(uintptr_t)g_tmap_ring[0]) >> 7], 0u);
 }
 
 }  // namespace udp
