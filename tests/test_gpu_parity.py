@@ -412,3 +412,40 @@ def test_decode_nonfinite_maps_inside_a_stream(impl, orc):
     assert np.array_equal(np.isnan(a["preds"]), np.isnan(b["preds"]))
     ok = ~np.isnan(a["preds"])
     assert np.abs(a["preds"][ok] - b["preds"][ok]).max() <= 1e-4
+
+
+def test_full_size_batch_independence(impl):
+    """At the bench's full size (16 384 persons, cfg 2: 20 GB of network outputs) every stage is
+    person-independent: one launch over the whole batch must return exactly what eight launches over
+    its 2 048-person chunks return (the small-N chunks are what the oracle tests pin), and the
+    decoded keypoints of a map must not depend on which CTA of the persistent grid met it."""
+    import torch
+    from udp_pose_b200 import device_api as D
+    cfg = CONFIGS[2]
+    N, C = 16384, 2048
+    W, H = cfg.image_size
+    w, h = cfg.heatmap_size
+    rng = np.random.default_rng(2024)
+    c, s, r = synth.boxes(cfg, N, rng, rotate=True)
+    imgs = torch.from_numpy(synth.source_images(8, rng)).cuda()
+    idx = np.arange(N) % 8
+    j, v = synth.joints(cfg, N, rng)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    out = torch.rand((N, cfg.channels, h, w), device="cuda", generator=g)
+    fl = torch.rand((N, cfg.channels, h, w), device="cuda", generator=g)
+    cd, sd, rd = (torch.from_numpy(a).cuda() for a in (c, s, r))
+    M = D.warp_matrices(cd, sd, rd, (W, H))
+    crop = D.crop_batch(D.SourceImages(imgs, idx), M, (W, H))
+    jd, vd = torch.from_numpy(j).cuda(), torch.from_numpy(v).cuda()
+    tgt, tw = D.encode_batch(cfg, jd, vd)
+    dec = D.decode_batch(cfg, out, fl, cd, sd, want_idx=True)
+    for lo in range(0, N, C):
+        sl = slice(lo, lo + C)
+        Mc = D.warp_matrices(cd[sl], sd[sl], rd[sl], (W, H))
+        assert torch.equal(Mc, M[sl])
+        assert torch.equal(D.crop_batch(D.SourceImages(imgs, idx[sl]), Mc, (W, H)), crop[sl])
+        t2, w2 = D.encode_batch(cfg, jd[sl], vd[sl])
+        assert torch.equal(t2, tgt[sl]) and torch.equal(w2, tw[sl])
+        d2 = D.decode_batch(cfg, out[sl], fl[sl], cd[sl], sd[sl], want_idx=True)
+        for k in ("preds", "maxvals", "preds_in", "idx"):
+            assert torch.equal(d2[k], dec[k][sl]), k
