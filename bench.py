@@ -505,14 +505,25 @@ def run_ours(args):
         pipe.synchronize()
         stream_s = time.perf_counter() - ts
         barrier()
+        tsr = torch.tensor([stream_s], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tsr, op=dist.ReduceOp.MAX)
+        stream_s = float(tsr[0])
         e2e = {"value": world * nb * e_steps / (float(te[0]) * 1e-3), "unit": UNIT,
-               "streaming_value": round(nb * e_steps / stream_s, 1),
+               "streaming_value": round(world * nb * e_steps / stream_s, 1),
                "h2d_bytes_per_step": hb.h2d_bytes(), "d2h_bytes_per_step": hb.d2h_bytes(),
                "persons_per_step_per_gpu": nb, "steps": e_steps, "chunk": args.e2e_chunk,
                "api": "udp_pose_b200.pipeline.HostPipeline.run (pinned host in -> H2D -> 5 kernels via the C ABI -> D2H: crop, target, target_weight, keypoints)",
                "launches": pipe.launches}
-        if world == 1:
-            e2e["link"] = link_ceiling(torch, hb.h2d_bytes() // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk)
+        # what the host links alone allow, all ranks copying at the same time (no kernels)
+        barrier()
+        link = link_ceiling(torch, hb.h2d_bytes() // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk)
+        lt = torch.tensor([link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"]], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(lt, op=dist.ReduceOp.SUM)
+            link["note"] += "; summed over the %d ranks, which copy concurrently" % world
+        link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"] = (round(float(v), 1) for v in lt)
+        e2e["link"] = link
 
     if rank != 0:
         if world > 1:
