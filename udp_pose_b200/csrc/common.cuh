@@ -122,6 +122,21 @@ __device__ __forceinline__ f32x2 ffma2pp(f32x2 a, f32x2 b, f32x2 c)
     return d;
 }
 
+// Wait until the mbarrier at shared address `mbar` completes the phase of parity `parity`
+// (try_wait suspends the thread in hardware between polls).
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "UDP_MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra UDP_MBAR_DONE;\n"
+        "bra UDP_MBAR_WAIT;\n"
+        "UDP_MBAR_DONE:\n"
+        "}\n" ::"r"(mbar), "r"(parity) : "memory");
+}
+
 // center/scale loader honouring the caller's dtype.
 struct CS {
     double c0, c1;   // center as double (exact widening when float32)

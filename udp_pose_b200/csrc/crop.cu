@@ -14,12 +14,12 @@
 // rint(M00*x*1024), rint(M10*x*1024) and the per-row bases are float64 and are computed
 // once per CTA into shared memory; the per-pixel work is integer only.  The finished
 // ROWS x W x 3 byte tile is staged in shared memory and leaves as 16-byte streaming stores.
-#include <cuda.h>  // CUtensorMap and its enums (types only: the encoder is fetched with cudaGetDriverEntryPoint)
 #include <cmath>
 #include <cstring>
 #include <mutex>
 
 #include "decode_pipe.cuh"
+#include "tma_host.cuh"
 
 namespace udp {
 
@@ -597,19 +597,6 @@ __device__ __align__(128) unsigned char g_tmap_ring[TM_SLOTS][128];
 __device__ unsigned int g_tmap_next;
 __device__ unsigned int g_tmap_busy[TM_SLOTS];
 
-__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "UDP_MBAR_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra UDP_MBAR_DONE;\n"
-        "bra UDP_MBAR_WAIT;\n"
-        "UDP_MBAR_DONE:\n"
-        "}\n" ::"r"(mbar), "r"(parity) : "memory");
-}
-
 // ROWS rows (every fourth of a tile) of one warp: the taps of row i+1 are loaded before the
 // arithmetic, shuffles and store of row i.
 template <int ROWS, class OUT>
@@ -635,7 +622,9 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
                           const float *M, typename OUT::Args oargs, int W, int H)
 {
     // CT_NBOX boxes of CT_BOX bytes | 128 B descriptor | 32 B of mbarriers | int4 colc[W/32] | int2 rowq[H]
-    extern __shared__ __align__(128) unsigned char fp[];
+    // dynamic shared memory is only guaranteed 16-byte alignment; TMA destinations need 128
+    extern __shared__ __align__(16) unsigned char fp_raw[];
+    unsigned char *fp = fp_raw + ((128u - ((unsigned)__cvta_generic_to_shared(fp_raw) & 127u)) & 127u);  // still a shared-space pointer
     const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
     const unsigned sdesc = fpa + CT_SMEM, mbar = sdesc + 128;
     const int tiles_x = W / CT;
@@ -784,20 +773,10 @@ static int crop_tma_template(CUtensorMap *out)
     std::lock_guard<std::mutex> lock(mu);
     if (state == 0) {
         state = -1;
-        typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                      const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-        void *fn = nullptr, *ring = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && fn &&
-            q == cudaDriverEntryPointSuccess && cudaGetSymbolAddress(&ring, udp::g_tmap_ring) == cudaSuccess) {
-            const cuuint64_t gdim[2] = {4096, 4096}, gstride[1] = {4096};
-            const cuuint32_t box[2] = {64, 32}, estride[2] = {1, 1};
-            if (((encode_fn)fn)(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, ring, gdim, gstride, box, estride,
-                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
-                state = 1;
-        }
+        void *ring = nullptr;
+        if (cudaGetSymbolAddress(&ring, udp::g_tmap_ring) == cudaSuccess &&
+            udp::tma_make_2d(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, ring, 4096, 4096, 4096, 64, 32))
+            state = 1;
         (void)cudaGetLastError();
     }
     if (state == 1) *out = tm;
@@ -829,7 +808,7 @@ static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_
     CUtensorMap tmpl;
     const int tma = crop_tma_armed(&tmpl);
     if (tma) {  // persons whose images / boxes suit the TMA unit; the launch below does the others
-        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 160 + 16 * tiles_x + 8 * H, stream>>>(
+        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 160 + 16 * tiles_x + 8 * H + 128, stream>>>(
             tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
         UDP_LAUNCH_CHECK();
     }

@@ -297,14 +297,19 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
 // lanes per map while the other warps waited at the next barrier -- 37 % of stall samples were
 // barrier stalls, 19 % of all instructions were the tail).
 template <int W, int H, int NT, int MINB, bool POST, bool FLIP, bool DIV255>
-__global__ void __launch_bounds__(NT, MINB) decode_gaussian_pipe_kernel(DecodeGaussArgs p, long long maps)
+__global__ void __launch_bounds__(NT, MINB)
+decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_fl,
+                            DecodeGaussArgs p, long long maps)
 {
     constexpr int R = 3;
     using G = PipeGeom<W, H, R, NT>;
     constexpr int NW = G::NWARP;
     constexpr int B_MN = 7, B_MX = 7 + NW, B_BV = 7 + 2 * NW, B_BI = B_BV + 1, B_MAP = B_BV + 2;
     constexpr int BOXW = ((B_MAP + 1) | 1);  // odd stride: conflict-free entry-per-thread reads
-    extern __shared__ __align__(16) float smem[];
+    // dynamic shared memory is only guaranteed 16-byte alignment; TMA destinations need 128
+    extern __shared__ __align__(16) float smem_raw[];
+    float *smem = smem_raw + ((128u - ((unsigned)__cvta_generic_to_shared(smem_raw) & 127u)) & 127u) / 4u;  // still a shared-space pointer
+    __shared__ __align__(8) unsigned long long s_bars[3];
     __shared__ float s_wmax[NW];
     __shared__ int s_idx;
     constexpr int NBOX = 32;
@@ -314,14 +319,13 @@ __global__ void __launch_bounds__(NT, MINB) decode_gaussian_pipe_kernel(DecodeGa
     const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
     constexpr bool has_fl = FLIP;
 
-    PipePlan<W, H, R, NT> plan;
-    plan.init(smem);
+    PipeFeed<W, H, R, NT> feed;
+    feed.init(smem, s_bars);
     MapWalk nxt;  // (person, joint) of the map being prefetched
     nxt.init(blockIdx.x, (int)gridDim.x, p.K);
-    auto src_of = [&](long long m) { return p.hm + m * (long long)hw; };
-    auto fl_of = [&]() -> const float * {  // partner map of the map `nxt` points at
-        if (!has_fl) return nullptr;
-        return p.hm_flipped + ((long long)nxt.n * p.K + __ldg(p.flip_perm + nxt.k)) * (long long)hw;
+    auto row_of = [&](long long m) { return (int)(m * H); };  // first tensor row of map m
+    auto fl_row = [&]() {  // partner map of the map `nxt` points at
+        return (int)(((long long)nxt.n * p.K + __ldg(p.flip_perm + nxt.k)) * H);
     };
     auto flush = [&](int count) {  // executed by one full warp
         if (lane < count) {
@@ -345,20 +349,22 @@ __global__ void __launch_bounds__(NT, MINB) decode_gaussian_pipe_kernel(DecodeGa
     // buffer roles: bP holds out_i (then T_i), bN receives out_{i+1}; buffer 2 always holds the flipped map
     long long map = blockIdx.x;
     int bP = 0, bN = 1, slot = 0;
-    if (map < maps) {
-        pipe_prefetch<W, H, R, NT>(plan, bP, src_of(map));
-        if (has_fl) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+    if (map < maps && threadIdx.x == 0) {
+        feed.issue(bP, &tm_out, row_of(map));
+        if (has_fl) feed.issue(2, &tm_fl, fl_row());
     }
-    cp_async_commit();
     for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
         float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
-        cp_async_wait_all();
+        feed.wait(bP);
+        if (has_fl) feed.wait(2);
+        feed.release();
         __syncthreads();  // (A) this map has landed; the previous map's T (in bN) is dead
         const long long next = map + gridDim.x;
         nxt.advance();
-        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
-        cp_async_commit();
-        if (threadIdx.x == 0) s_idx = 0x7fffffff;
+        if (threadIdx.x == 0) {
+            if (next < maps) feed.issue(bN, &tm_out, row_of(next));
+            s_idx = 0x7fffffff;
+        }
         // mailbox full: one warp finishes the 32 queued maps.  No extra barrier: the next mailbox
         // write comes after barrier (C) of this iteration, which this warp has to pass too.
         if (slot == NBOX) {
@@ -376,19 +382,19 @@ __global__ void __launch_bounds__(NT, MINB) decode_gaussian_pipe_kernel(DecodeGa
         if (lane == 0) s_wmax[warp] = wm;
         const bool bad = !(fabsf(fs) < INFINITY);
         if (__syncthreads_or(bad)) {  // a non-finite value: NaN-exact generic path for this map
-            cp_async_wait_all();
+            if (next < maps) feed.wait(bN);  // the load in flight must land before the buffers are reused
             __syncthreads();
             decode_gauss_generic_map<POST>(p, smem, map);  // clobbers all three buffers
-            if (next < maps) {
-                pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
-                if (has_fl) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+            feed.release();
+            __syncthreads();
+            if (next < maps && threadIdx.x == 0) {
+                feed.issue(bN, &tm_out, row_of(next));
+                if (has_fl) feed.issue(2, &tm_fl, fl_row());
             }
-            cp_async_commit();
             continue;
         }
         // (B) both raw buffers are consumed: T may overwrite out_i, flipped_{i+1} may land in Q
-        if (has_fl && next < maps) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
-        cp_async_commit();
+        if (has_fl && next < maps && threadIdx.x == 0) feed.issue(2, &tm_fl, fl_row());
         float M = s_wmax[0];
 #pragma unroll
         for (int q = 1; q < NW; ++q) M = fmaxf(M, s_wmax[q]);
@@ -426,13 +432,12 @@ __global__ void __launch_bounds__(NT, MINB) decode_gaussian_pipe_kernel(DecodeGa
         }
         ++slot;
     }
-    cp_async_wait_all();
     __syncthreads();
     if (slot && warp == 0) flush(slot);
 }
 
 template <int W, int H, int NT, int MINB>
-static void (*pick_gauss_pipe(bool post, bool flip, bool div))(DecodeGaussArgs, long long)
+static void (*pick_gauss_pipe(bool post, bool flip, bool div))(CUtensorMap, CUtensorMap, DecodeGaussArgs, long long)
 {
 #define UDP_PICK(P, F, D) if (post == P && flip == F && div == D) return decode_gaussian_pipe_kernel<W, H, NT, MINB, P, F, D>;
     UDP_PICK(true, true, false) UDP_PICK(true, false, false) UDP_PICK(true, true, true) UDP_PICK(true, false, true)
@@ -482,20 +487,24 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
     // blurred write-back.  Everything else (and every map holding a NaN/inf) runs the generic code.
     if (!udp_force_generic() && !blurred && (pre_div == 0.0f || pre_div == 255.0f)) {
 #define UDP_GAUSS_PIPE(WW, HH, NT, MINB)                                                             \
-        if (w == WW && h == HH) {                                                                \
+        if (w == WW && h == HH) do {                                                             \
             using G = udp::PipeGeom<WW, HH, 3, NT>;                                              \
-            const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
-            void (*kern)(udp::DecodeGaussArgs, long long) = udp::pick_gauss_pipe<WW, HH, NT, MINB>(      \
-                post_process != 0, hm_flipped != nullptr, pre_div != 0.0f);                      \
+            const size_t smem = (G::SMEM > gsmem ? G::SMEM : gsmem) + 128;  /* + alignment slack */ \
+            void (*kern)(CUtensorMap, CUtensorMap, udp::DecodeGaussArgs, long long) =                   \
+                udp::pick_gauss_pipe<WW, HH, NT, MINB>(post_process != 0, hm_flipped != nullptr, pre_div != 0.0f); \
+            CUtensorMap tm_out, tm_fl;                                                           \
+            const bool tma_ok = udp::pipe_make_map(&tm_out, hm, WW, HH, G::SR, maps) &&          \
+                                udp::pipe_make_map(&tm_fl, hm_flipped ? hm_flipped : hm, WW, HH, G::SR, maps); \
+            if (!tma_ok) break;  /* no tensor-map encoder: the generic kernel below */          \
             int per_sm = 0;                                                                      \
             int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
             if (rc) return rc;                                                                   \
             long long grid = (long long)per_sm * udp::sm_count();                                \
             if (grid > maps) grid = maps;                                                        \
-            kern<<<(unsigned)grid, NT, smem, (cudaStream_t)stream>>>(a, maps);                   \
+            kern<<<(unsigned)grid, NT, smem, (cudaStream_t)stream>>>(tm_out, tm_fl, a, maps);    \
             UDP_LAUNCH_CHECK();                                                                  \
             return 0;                                                                            \
-        }
+        } while (0);
         UDP_GAUSS_PIPE(48, 64, 96, 4)
         UDP_GAUSS_PIPE(64, 64, 128, 3)
         UDP_GAUSS_PIPE(72, 96, 288, 2)

@@ -212,27 +212,32 @@ __device__ __forceinline__ void offset_final(const DecodeOffsetArgs &p, long lon
 // after the next barrier one warp finishes the 32 maps, one per lane.  Maps holding a
 // non-finite value are re-done by the generic path above (np.argmax's NaN rule).
 template <int W, int H, int NT, int MINB, bool FLIP>
-__global__ void __launch_bounds__(NT, MINB) decode_offset_pipe_kernel(DecodeOffsetArgs p, long long maps)
+__global__ void __launch_bounds__(NT, MINB)
+decode_offset_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_fl,
+                          DecodeOffsetArgs p, long long maps)
 {
     constexpr int R = 7;
     using G = PipeGeom<W, H, R, NT>;
     constexpr int NW = G::NWARP, NBOX = 32;
     constexpr int B_V = 0, B_I = NW, B_MAP = 2 * NW, BOXW = 2 * NW + 1;
-    extern __shared__ __align__(16) float smem[];
+    // dynamic shared memory is only guaranteed 16-byte alignment; TMA destinations need 128
+    extern __shared__ __align__(16) float smem_raw[];
+    float *smem = smem_raw + ((128u - ((unsigned)__cvta_generic_to_shared(smem_raw) & 127u)) & 127u) / 4u;  // still a shared-space pointer
+    __shared__ __align__(8) unsigned long long s_bars[3];
     __shared__ float s_box[NBOX * BOXW];
     __shared__ float s_rows[NBOX * 14];
     constexpr int hw = H * W;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
 
-    PipePlan<W, H, R, NT> plan;
-    plan.init(smem);
+    PipeFeed<W, H, R, NT> feed;
+    feed.init(smem, s_bars);
     MapWalk nxt;  // (person, joint) of the map being prefetched
     nxt.init(blockIdx.x, (int)gridDim.x, p.K);
     auto src_of = [&](long long m) { return p.out + (m * 3) * (long long)hw; };
-    auto fl_of = [&]() -> const float * {  // partner map of the map `nxt` points at
-        if (!FLIP) return nullptr;
-        return p.out_flipped + (((long long)nxt.n * p.K + __ldg(p.flip_perm + nxt.k)) * 3) * (long long)hw;
+    auto row_of = [&](long long m) { return (int)(m * 3 * H); };  // first tensor row of the classification map of joint map m
+    auto fl_row = [&]() {  // partner map of the map `nxt` points at
+        return (int)((((long long)nxt.n * p.K + __ldg(p.flip_perm + nxt.k)) * 3) * H);
     };
     auto entry = [&](int e, float &bv, int &bi) -> long long {  // combine the per-warp candidates
         const float *b = s_box + e * BOXW;
@@ -267,19 +272,19 @@ __global__ void __launch_bounds__(NT, MINB) decode_offset_pipe_kernel(DecodeOffs
     // buffer roles: bP holds out_i (then T_i), bN receives out_{i+1}; buffer 2 always holds the flipped map
     long long map = blockIdx.x;
     int bP = 0, bN = 1, slot = 0;
-    if (map < maps) {
-        pipe_prefetch<W, H, R, NT>(plan, bP, src_of(map));
-        if (FLIP) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+    if (map < maps && threadIdx.x == 0) {
+        feed.issue(bP, &tm_out, row_of(map));
+        if (FLIP) feed.issue(2, &tm_fl, fl_row());
     }
-    cp_async_commit();
     for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
         float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
-        cp_async_wait_all();
+        feed.wait(bP);
+        if (FLIP) feed.wait(2);
+        feed.release();
         __syncthreads();  // (A) this map has landed; the previous map's T (in bN) is dead
         const long long next = map + gridDim.x;
         nxt.advance();
-        if (next < maps) pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
-        cp_async_commit();
+        if (next < maps && threadIdx.x == 0) feed.issue(bN, &tm_out, row_of(next));
         // mailbox full: everyone gathers offset rows now; warp 0 finishes the maps after barrier (B).
         // No extra barrier: the next mailbox / s_rows write comes after (C), resp. the next flush.
         const bool finish = slot == NBOX;
@@ -294,23 +299,22 @@ __global__ void __launch_bounds__(NT, MINB) decode_offset_pipe_kernel(DecodeOffs
         const bool anybad = __syncthreads_or(bad);
         if (finish && warp == 0) flush_final(NBOX);
         if (anybad) {  // NaN / inf somewhere in the map
-            cp_async_wait_all();
+            if (next < maps) feed.wait(bN);  // the load in flight must land before the buffers are reused
             __syncthreads();
             const int gn = (int)(map / p.K), gk = (int)(map - (long long)gn * p.K);
             const float *gfl = FLIP ? p.out_flipped + (((long long)gn * p.K + p.flip_perm[gk]) * 3) * (long long)hw
                                     : nullptr;
             decode_offset_generic(p, smem, map, gn, src_of(map), gfl);  // clobbers all three buffers
+            feed.release();
             __syncthreads();
-            if (next < maps) {
-                pipe_prefetch<W, H, R, NT>(plan, bN, src_of(next));
-                if (FLIP) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
+            if (next < maps && threadIdx.x == 0) {
+                feed.issue(bN, &tm_out, row_of(next));
+                if (FLIP) feed.issue(2, &tm_fl, fl_row());
             }
-            cp_async_commit();
             continue;
         }
         // (B) both raw buffers are consumed: T may overwrite out_i, flipped_{i+1} may land in Q
-        if (FLIP && next < maps) pipe_prefetch<W, H, R, NT>(plan, 2, fl_of());
-        cp_async_commit();
+        if (FLIP && next < maps && threadIdx.x == 0) feed.issue(2, &tm_fl, fl_row());
         float *T = bufP;
         pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
         __syncthreads();  // (C) T complete
@@ -335,7 +339,6 @@ __global__ void __launch_bounds__(NT, MINB) decode_offset_pipe_kernel(DecodeOffs
         if (threadIdx.x == 0) box[B_MAP] = __int_as_float((int)map);
         ++slot;
     }
-    cp_async_wait_all();
     __syncthreads();
     if (slot) {
         flush_rows(slot);
@@ -365,21 +368,25 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
     if (gsmem > 200 * 1024) return UDP_EINVAL;
     if (!udp_force_generic()) {
 #define UDP_OFF_PIPE(WW, HH, NT, MINB)                                                               \
-        if (w == WW && h == HH) {                                                                \
+        if (w == WW && h == HH) do {                                                             \
             using G = udp::PipeGeom<WW, HH, 7, NT>;                                              \
-            const size_t smem = G::SMEM > gsmem ? G::SMEM : gsmem;                               \
-            void (*kern)(udp::DecodeOffsetArgs, long long) =                                     \
+            const size_t smem = (G::SMEM > gsmem ? G::SMEM : gsmem) + 128;  /* + alignment slack */ \
+            void (*kern)(CUtensorMap, CUtensorMap, udp::DecodeOffsetArgs, long long) =           \
                 out_flipped ? udp::decode_offset_pipe_kernel<WW, HH, NT, MINB, true>             \
                             : udp::decode_offset_pipe_kernel<WW, HH, NT, MINB, false>;           \
+            CUtensorMap tm_out, tm_fl;  /* [3K maps per person][H][W]; the kernel loads every third map */ \
+            const bool tma_ok = udp::pipe_make_map(&tm_out, out, WW, HH, G::SR, 3 * maps) &&     \
+                                udp::pipe_make_map(&tm_fl, out_flipped ? out_flipped : out, WW, HH, G::SR, 3 * maps); \
+            if (!tma_ok) break;  /* no tensor-map encoder: the generic kernel below */          \
             int per_sm = 0;                                                                      \
             int rc = udp::persistent_grid((const void *)kern, NT, smem, &per_sm);                \
             if (rc) return rc;                                                                   \
             long long grid = (long long)per_sm * udp::sm_count();                                \
             if (grid > maps) grid = maps;                                                        \
-            kern<<<(unsigned)grid, NT, smem, (cudaStream_t)stream>>>(a, maps);                   \
+            kern<<<(unsigned)grid, NT, smem, (cudaStream_t)stream>>>(tm_out, tm_fl, a, maps);    \
             UDP_LAUNCH_CHECK();                                                                  \
             return 0;                                                                            \
-        }
+        } while (0);
         UDP_OFF_PIPE(48, 64, 96, 4)
         UDP_OFF_PIPE(64, 64, 128, 3)
         UDP_OFF_PIPE(72, 96, 288, 2)

@@ -28,6 +28,7 @@
 // Maps holding a non-finite value are handed to the generic, NaN-exact code path.
 #pragma once
 #include "blur_fast.cuh"
+#include "tma_host.cuh"
 
 namespace udp {
 
@@ -85,7 +86,8 @@ struct PipeGeom {
     static constexpr int ST = W + 2;                      // T row stride
     static constexpr int TROWS = H + 2 * R;
     static constexpr int RAW = H * SR;                    // floats per raw tensor
-    static constexpr int BUF = (RAW > TROWS * ST) ? RAW : ((TROWS * ST + 3) / 4) * 4;  // one buffer
+    static constexpr int BUF0 = (RAW > TROWS * ST) ? RAW : TROWS * ST;
+    static constexpr int BUF = ((BUF0 + 31) / 32) * 32;   // one buffer, a multiple of 128 bytes (TMA destination)
     static constexpr size_t SMEM = (size_t)3 * BUF * sizeof(float);
     static constexpr int NWARP = (NT + 31) / 32;
 };
@@ -125,6 +127,56 @@ __device__ __forceinline__ void pipe_prefetch(const PipePlan<W, H, R, NT> &pl, i
     for (int j = 0; j < P::ITER; ++j)
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + (unsigned)(j * P::RPI * G::SR * 4)),
                      "l"(s0 + j * NT * 4) : "memory");
+}
+
+// The TMA feed of the pipeline: one tensor load per map instead of H*W/4 cp.async per tensor (which
+// cost the SM an LDGSTS + three filler issue slots each and a quarter of the kernels' shared-memory
+// wavefronts).  The network output is described as a 2-D float tensor [maps*H][W]; the box is
+// [H][SR]: the SR - W columns past the row end lie outside the tensor and are zero-filled, so a map
+// lands directly at the padded row stride the row pass wants.  One mbarrier per buffer; every
+// thread tracks the parities, thread 0 issues.
+template <int W, int H, int R, int NT>
+struct PipeFeed {
+    using G = PipeGeom<W, H, R, NT>;
+    static constexpr unsigned BYTES = (unsigned)(G::SR * H * 4);
+    unsigned smem0, bars, par;
+    __device__ __forceinline__ void init(const float *smem, unsigned long long *bar_storage)
+    {
+        smem0 = (unsigned)__cvta_generic_to_shared(smem);
+        bars = (unsigned)__cvta_generic_to_shared(bar_storage);
+        par = 0u;
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int i = 0; i < 3; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8 * i) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+    }
+    // one thread: arm the barrier of `buf` and start the load of the map whose first row is `row`
+    __device__ __forceinline__ void issue(int buf, const CUtensorMap *tm, int row) const
+    {
+        const unsigned bar = bars + 8 * buf;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(BYTES) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                     ::"r"(smem0 + (unsigned)buf * (unsigned)(G::BUF * 4)), "l"((unsigned long long)(uintptr_t)tm), "r"(0), "r"(row), "r"(bar)
+                     : "memory");
+    }
+    // every thread: the load into `buf` has landed
+    __device__ __forceinline__ void wait(int buf)
+    {
+        mbar_wait(bars + 8 * buf, (par >> buf) & 1u);
+        par ^= 1u << buf;
+    }
+    // every thread, before the barrier that precedes a refill: order this thread's shared-memory
+    // writes (T) before the asynchronous-proxy write of the next load
+    static __device__ __forceinline__ void release() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+};
+
+inline bool pipe_make_map(CUtensorMap *tm, const float *base, int W, int H, int SR, long long maps)
+{
+    if (maps * H >= 0x7fffffffLL) return false;  // row coordinates are int32
+    return tma_make_2d(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, (unsigned long long)W, (unsigned long long)(maps * H),
+                       (unsigned long long)W * 4, (unsigned)SR, (unsigned)H);
 }
 
 // (person, joint) of a map index that advances by a fixed step, without 64-bit divisions.
