@@ -6,12 +6,13 @@
 // 36-48 % issue-active, 20-30 % of DRAM peak), and ~8000 warp-instructions per 64x48 map.
 //
 // This version:
-//  * persistent CTAs (a few per SM) walk the (person, joint) maps with a cp.async pipeline:
-//    while map i is being decoded, the 16-byte asynchronous copies of map i+1 (and of its
-//    mirrored partner map) are already in flight.  Three buffers rotate: P holds out_i and,
+//  * persistent CTAs (a few per SM) walk the (person, joint) maps with a TMA pipeline (third
+//    generation; the second used 16-byte cp.async copies, see PipeFeed below): while map i is
+//    being decoded, the tensor loads of map i+1 (and of its mirrored partner map) are in flight.
+//    Three buffers rotate: P holds out_i and,
 //    once the row pass has consumed it, T_i; Q holds flipped_i and is refilled with
 //    flipped_{i+1} as soon as the row pass has read it; N receives out_{i+1} and becomes the
-//    next P.  The copies place each row at a padded stride (SR/4 odd) so that the later per-row
+//    next P.  The loads place each row at a padded stride (SR/4 odd) so that the later per-row
 //    LDS.128 reads are bank-conflict free; no thread holds HBM data in registers while waiting.
 //  * the flip test ((out + mirror(partner)) * 0.5, utils/transforms.py:15-47 +
 //    core/function.py:171) is fused into the ROW pass: a thread owns two rows (p, p + H/2) and a
@@ -91,43 +92,6 @@ struct PipeGeom {
     static constexpr size_t SMEM = (size_t)3 * BUF * sizeof(float);
     static constexpr int NWARP = (NT + 31) / 32;
 };
-
-// Asynchronous copy of one map (and its flip partner) into a stage, rows at stride SR.
-// A thread copies the same 16-byte column chunk of every (NT / (W/4))-th row, so source and
-// destination offsets are a per-thread constant plus compile-time immediates (the first build
-// recomputed row/column by division for each of the 32 copies: ~100 integer instructions
-// per thread and map).
-template <int W, int H, int R, int NT>
-struct PipePlan {
-    using G = PipeGeom<W, H, R, NT>;
-    static constexpr int W4 = W / 4;
-    static_assert(NT % W4 == 0, "NT must be a multiple of W/4");
-    static constexpr int RPI = NT / W4;  // rows per iteration
-    static_assert(H % RPI == 0, "H must be a multiple of NT/(W/4)");
-    static constexpr int ITER = H / RPI;
-    unsigned dst;  // shared-space byte address inside buffer 0
-    unsigned src;  // float offset inside the map
-    __device__ __forceinline__ void init(const float *smem_base)
-    {
-        const int ty = threadIdx.x / W4, tx = threadIdx.x - ty * W4;
-        dst = (unsigned)__cvta_generic_to_shared(smem_base) + (unsigned)(ty * G::SR + tx * 4) * 4u;
-        src = threadIdx.x * 4;
-    }
-};
-
-// one tensor (H x W floats at `src`) -> buffer `buf` (0..2), rows at stride SR
-template <int W, int H, int R, int NT>
-__device__ __forceinline__ void pipe_prefetch(const PipePlan<W, H, R, NT> &pl, int buf, const float *__restrict__ src)
-{
-    using G = PipeGeom<W, H, R, NT>;
-    using P = PipePlan<W, H, R, NT>;
-    const unsigned d0 = pl.dst + (unsigned)buf * (unsigned)(G::BUF * 4);
-    const float *s0 = src + pl.src;
-#pragma unroll
-    for (int j = 0; j < P::ITER; ++j)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + (unsigned)(j * P::RPI * G::SR * 4)),
-                     "l"(s0 + j * NT * 4) : "memory");
-}
 
 // The TMA feed of the pipeline: one tensor load per map instead of H*W/4 cp.async per tensor (which
 // cost the SM an LDGSTS + three filler issue slots each and a quarter of the kernels' shared-memory
