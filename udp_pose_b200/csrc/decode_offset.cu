@@ -206,7 +206,7 @@ __device__ __forceinline__ void offset_final(const DecodeOffsetArgs &p, long lon
 }
 
 // Streaming fast path (decode_pipe.cuh): persistent CTAs, 2-stage cp.async pipeline over the
-// classification maps, 15x15 packed-FP32 blur, arg-max on the blurred map.  Three barriers per
+// classification maps, 15x15 packed-FP32 blur, arg-max on the blurred map.  Two barriers per
 // map; the per-warp arg-max candidates go to a 32-entry mailbox.  Every 32 maps all threads
 // share the 32 x 14 offset-window rows (scattered global loads, all in flight together), and
 // after the next barrier one warp finishes the 32 maps, one per lane.  Maps holding a
@@ -278,17 +278,15 @@ decode_offset_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
     }
     for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
         float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
-        feed.wait(bP);
+        feed.wait(bP);  // per-thread wait: no CTA barrier is needed to read a landed map
         if (FLIP) feed.wait(2);
-        feed.release();
-        __syncthreads();  // (A) this map has landed; the previous map's T (in bN) is dead
         const long long next = map + gridDim.x;
         nxt.advance();
-        if (next < maps && threadIdx.x == 0) feed.issue(bN, &tm_out, row_of(next));
-        // mailbox full: everyone gathers offset rows now; warp 0 finishes the maps after barrier (B).
-        // No extra barrier: the next mailbox / s_rows write comes after (C), resp. the next flush.
+        // mailbox full: everyone gathers offset rows now (one barrier so that the last entry is
+        // visible); warp 0 finishes the maps after barrier (B).  The next mailbox / s_rows write
+        // comes after (C), resp. the next flush.
         const bool finish = slot == NBOX;
-        if (finish) { flush_rows(NBOX); slot = 0; }
+        if (finish) { __syncthreads(); flush_rows(NBOX); slot = 0; }
 
         f32x2 v[G::NCOL];
         pipe_window<W, H, R, NT, FLIP, false>(bufP, bufQ, pr, xs, v);
@@ -296,7 +294,11 @@ decode_offset_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
 #pragma unroll
         for (int j = G::PAD; j < G::PAD + G::SEG; j += 2) acc = fadd2p(acc, fadd2p(v[j], v[j + 1]));
         const bool bad = !(fabsf(lo_of(acc) + hi_of(acc)) < INFINITY);
+        feed.release();  // this thread's T_{i-1} stores (in bN) are ordered before the bulk load below
+        // (B) both raw buffers are consumed and everyone has left the previous column pass:
+        // out_{i+1} may land in bN (it held T_{i-1}), T_i may overwrite out_i, flipped_{i+1} may land in Q
         const bool anybad = __syncthreads_or(bad);
+        if (next < maps && threadIdx.x == 0) feed.issue(bN, &tm_out, row_of(next));
         if (finish && warp == 0) flush_final(NBOX);
         if (anybad) {  // NaN / inf somewhere in the map
             if (next < maps) feed.wait(bN);  // the load in flight must land before the buffers are reused
@@ -313,7 +315,6 @@ decode_offset_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
             }
             continue;
         }
-        // (B) both raw buffers are consumed: T may overwrite out_i, flipped_{i+1} may land in Q
         if (FLIP && next < maps && threadIdx.x == 0) feed.issue(2, &tm_fl, fl_row());
         float *T = bufP;
         pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
