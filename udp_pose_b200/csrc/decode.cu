@@ -289,8 +289,8 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
 // ---------------------------------------------------------------------------------------
 // Streaming fast path (decode_pipe.cuh): persistent CTAs, 2-stage cp.async pipeline.
 // ---------------------------------------------------------------------------------------
-// Per map only three barriers remain: (A) data landed, (B) raw stage consumed / warp maxima
-// published, (C) T complete.  Everything that is serial per map -- min/max combine, the float64
+// Per map only two barriers remain: (B) raw stage consumed / warp maxima published, (C) T
+// complete (a landed map is read after a per-thread mbarrier wait, no CTA barrier).  Everything that is serial per map -- min/max combine, the float64
 // log + Taylor + 2x2 solve, the inverse affine and the result stores -- is deferred: each map
 // leaves 7 tap values, per-warp min/max, maxval and index in a shared-memory mailbox, and every 32
 // maps the 32 lanes of one warp finish one mailbox entry each (first build: that tail ran on 7
@@ -311,7 +311,7 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
     float *smem = smem_raw + ((128u - ((unsigned)__cvta_generic_to_shared(smem_raw) & 127u)) & 127u) / 4u;  // still a shared-space pointer
     __shared__ __align__(8) unsigned long long s_bars[3];
     __shared__ float s_wmax[NW];
-    __shared__ int s_idx;
+    __shared__ int s_idx[2];  // first index of the maximum, one slot per raw buffer
     constexpr int NBOX = 32;
     __shared__ float s_box[NBOX * BOXW];
     constexpr int hw = H * W;
@@ -352,22 +352,19 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
     if (map < maps && threadIdx.x == 0) {
         feed.issue(bP, &tm_out, row_of(map));
         if (has_fl) feed.issue(2, &tm_fl, fl_row());
+        s_idx[bP] = 0x7fffffff;  // visible to the first atomicMin through barrier (B)
     }
     for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
         float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
-        feed.wait(bP);
+        feed.wait(bP);  // per-thread wait: no CTA barrier is needed to read a landed map
         if (has_fl) feed.wait(2);
-        feed.release();
-        __syncthreads();  // (A) this map has landed; the previous map's T (in bN) is dead
         const long long next = map + gridDim.x;
         nxt.advance();
-        if (threadIdx.x == 0) {
-            if (next < maps) feed.issue(bN, &tm_out, row_of(next));
-            s_idx = 0x7fffffff;
-        }
-        // mailbox full: one warp finishes the 32 queued maps.  No extra barrier: the next mailbox
-        // write comes after barrier (C) of this iteration, which this warp has to pass too.
+        // mailbox full: one warp finishes the 32 queued maps (one barrier so that the last entry is
+        // visible).  The next mailbox write comes after barrier (C) of this iteration, which this
+        // warp has to pass too.
         if (slot == NBOX) {
+            __syncthreads();
             if (warp == 0) flush(NBOX);
             slot = 0;
         }
@@ -381,7 +378,15 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
         for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
         if (lane == 0) s_wmax[warp] = wm;
         const bool bad = !(fabsf(fs) < INFINITY);
-        if (__syncthreads_or(bad)) {  // a non-finite value: NaN-exact generic path for this map
+        feed.release();  // this thread's T_{i-1} stores (in bN) are ordered before the bulk load below
+        // (B) both raw buffers are consumed and everyone has left the previous column pass:
+        // out_{i+1} may land in bN (it held T_{i-1}), T_i may overwrite out_i, flipped_{i+1} may land in Q
+        const bool anybad = __syncthreads_or(bad);
+        if (threadIdx.x == 0) {
+            if (next < maps) feed.issue(bN, &tm_out, row_of(next));
+            s_idx[bN] = 0x7fffffff;  // the next map's slot; its last reader passed (B) with us
+        }
+        if (anybad) {  // a non-finite value: NaN-exact generic path for this map
             if (next < maps) feed.wait(bN);  // the load in flight must land before the buffers are reused
             __syncthreads();
             decode_gauss_generic_map<POST>(p, smem, map);  // clobbers all three buffers
@@ -393,17 +398,16 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
             }
             continue;
         }
-        // (B) both raw buffers are consumed: T may overwrite out_i, flipped_{i+1} may land in Q
         if (has_fl && next < maps && threadIdx.x == 0) feed.issue(2, &tm_fl, fl_row());
         float M = s_wmax[0];
 #pragma unroll
         for (int q = 1; q < NW; ++q) M = fmaxf(M, s_wmax[q]);
-        if (lm == M) atomicMin(&s_idx, pipe_first_index<W, H, R, NT>(v, M, pr, xs));
+        if (lm == M) atomicMin(&s_idx[bP], pipe_first_index<W, H, R, NT>(v, M, pr, xs));
         float *T = bufP;
         if (POST) pipe_row_filter<W, H, R, NT>(v, T, pr, xs);
         __syncthreads();  // (C) T complete, s_idx final
         float *box = s_box + slot * BOXW;
-        const int bi = s_idx;
+        const int bi = s_idx[bP];
         if (POST) {
             if (warp == NW - 1 && lane < 7) {  // the seven taps of the Taylor step (:100-109), edge-replicated
                 const int tdy[7] = {0, 0, 0, 1, -1, 1, -1};
