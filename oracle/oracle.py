@@ -98,6 +98,101 @@ def accuracy_pck(output, target, thr=0.5):
     return acc, avg, cnt, pred
 
 
+COCO_SIGMAS = np.array([.26, .25, .25, .35, .35, .79, .79, .72, .72, .62, .62, 1.07, 1.07, .87, .87, .89, .89]) / 10.0
+
+
+def coco_rescore(preds, box_score, in_vis_thre):
+    """SURVEY 8(f)-3, rescoring of deep_hrnet/lib/dataset/coco.py:326-339: mean of the joint scores above
+    `in_vis_thre` (accumulated in float32 in joint order, as the reference's scalar loop over a float32
+    record does) times the box score (float64).  preds f32 [N,K,3], box_score f64 [N] -> f64 [N]."""
+    preds = np.asarray(preds, np.float32)
+    out = np.zeros(len(preds))
+    for n in range(len(preds)):
+        acc, cnt = np.float32(0), 0
+        for t in preds[n, :, 2]:
+            if t > in_vis_thre:
+                acc, cnt = np.float32(acc + t), cnt + 1
+        mean = np.float32(acc / np.float32(cnt)) if cnt else 0
+        out[n] = mean * np.float64(box_score[n])
+    return out
+
+
+def oks_row(preds, area, i, rest, sigmas=None, in_vis_thre=None):
+    """oks_iou of lib/nms/nms.py:75-94 between person i and persons `rest` of one image: float32
+    coordinate differences and squares, float64 from the division by vars on, np.exp, and np.sum's
+    pairwise order over the K (or the masked) joints.  The optional mask keeps joints whose score
+    in the *candidate* is above in_vis_thre (`list(a) and list(b)` at :89 evaluates to list(b))."""
+    sig = COCO_SIGMAS if sigmas is None else np.asarray(sigmas, np.float64)
+    var = (sig * 2) ** 2
+    g = preds[i]
+    out = np.zeros(len(rest))
+    for k, r in enumerate(rest):
+        d = preds[r]
+        dx, dy = d[:, 0] - g[:, 0], d[:, 1] - g[:, 1]
+        e = (dx * dx + dy * dy) / var / ((area[i] + area[r]) / 2 + np.spacing(1)) / 2
+        if in_vis_thre is not None:
+            e = e[d[:, 2] > in_vis_thre]
+        out[k] = np.sum(np.exp(-e)) / e.shape[0] if e.shape[0] else 0.0
+    return out
+
+
+def _order_desc(scores):
+    """`scores.argsort()[::-1]` (nms.py:113): descending; among equal scores the higher row first,
+    which is what reversing a stable ascending sort gives (numpy's default sort leaves tie order
+    unspecified; the fixtures have no ties)."""
+    return np.argsort(scores, kind="stable")[::-1]
+
+
+def oks_nms(preds, area, score, thresh, sigmas=None, in_vis_thre=None):
+    """oks_nms of lib/nms/nms.py:97-124 for ONE image; returns the kept rows in keep order."""
+    preds = np.asarray(preds, np.float32)
+    order = _order_desc(np.asarray(score, np.float64))
+    keep = []
+    while order.size:
+        i = order[0]
+        keep.append(int(i))
+        ovr = oks_row(preds, area, i, order[1:], sigmas, in_vis_thre)
+        order = order[1:][ovr <= thresh]
+    return keep
+
+
+def soft_oks_nms(preds, area, score, thresh, sigmas=None, in_vis_thre=None, max_dets=20):
+    """soft_oks_nms of lib/nms/nms.py:139-180 (gaussian rescore :127-136) for ONE image.  The full
+    re-sort of every round only matters through its head, so each round takes the arg-max of the
+    decayed scores."""
+    preds = np.asarray(preds, np.float32)
+    score = np.asarray(score, np.float64)
+    order = _order_desc(score)
+    s = score[order]
+    keep = []
+    while order.size and len(keep) < max_dets:
+        i = order[0]
+        ovr = oks_row(preds, area, i, order[1:], sigmas, in_vis_thre)
+        s = s[1:] * np.exp(-ovr ** 2 / thresh)
+        order = order[1:]
+        t = np.argsort(s, kind="stable")[::-1]
+        order, s = order[t], s[t]
+        keep.append(int(i))
+    return keep
+
+
+def coco_rescore_nms(preds, all_boxes, image_ids, in_vis_thre, oks_thre, soft=False):
+    """coco.py:308-356: group the persons by image (first-appearance order, rows in input order),
+    rescore, then oks_nms / soft_oks_nms per image.  Returns (score f64 [N], [kept global rows per image])."""
+    preds = np.asarray(preds, np.float32)
+    score = coco_rescore(preds, all_boxes[:, 5], in_vis_thre)
+    groups = {}
+    for r, im in enumerate(image_ids):
+        groups.setdefault(int(im), []).append(r)
+    kept = []
+    for rows in groups.values():
+        rows = np.asarray(rows)
+        fn = soft_oks_nms if soft else oks_nms
+        k = fn(preds[rows], all_boxes[rows, 4], score[rows], oks_thre)
+        kept.append([int(rows[j]) for j in k])
+    return score, kept
+
+
 def to_tensor_normalize(crop, mean, std):
     """`transforms.Compose([ToTensor(), Normalize(mean, std)])` on the uint8 HWC crop
     (deep_hrnet/tools/train.py:127-143, applied at JointsDataset.py:237-238).  The transforms live
