@@ -160,6 +160,31 @@ int udp_accuracy_pck(const float *output, const float *target, int ch_stride, in
                      int N, double thr, float *pred, double *dists, double *acc, double *avg_acc,
                      int32_t *cnt, void *stream);
 
+/* SURVEY 8(f)-3  COCO rescoring: deep_hrnet/lib/dataset/coco.py:326-339.
+ *     preds [N,K,3] float32 (x, y, maxval -- the rows of validate()'s all_preds, function.py:208-209),
+ *     box_score [N] float64 (all_boxes[:,5]).  score[n] = mean(maxval > in_vis_thre) * box_score[n]
+ *     (float32 mean in joint order, float64 product; 0 when no joint passes). */
+int udp_coco_rescore(const float *preds, const double *box_score, int K, int N, double in_vis_thre,
+                     double *score, void *stream);
+
+/* SURVEY 8(f)-3  oks_nms / soft_oks_nms of deep_hrnet/lib/nms/nms.py:97-124 / :139-180 (with oks_iou
+ *     :75-94 and rescore :127-136), one CTA per image.  Persons of image i are rows
+ *     img_off[i] .. img_off[i+1]-1 of preds/area/score (img_off [num_images+1] int32; the caller groups
+ *     them, as coco.py:317-319 does); max_per_image >= the largest group (sizes shared memory).
+ *     area [N] float64 (all_boxes[:,4]), score [N] float64 (udp_coco_rescore's output).
+ *     sigmas_host: HOST pointer to K float64 (already divided by 10, as the reference's `sigmas`
+ *     argument is) or NULL = COCO's 17 defaults (nms.py:77).  use_vis_thre/in_vis_thre: oks_iou's
+ *     optional in_vis_thre (None in COCO evaluation => use_vis_thre = 0).  soft = 0: keep while
+ *     oks <= thresh; soft = 1: gaussian score decay, at most max_dets (20 at nms.py:158) per image.
+ *     Out: keep [N] int32 -- for image i, keep_cnt[i] global rows in the reference's keep order,
+ *     starting at keep[img_off[i]]; keep_cnt [num_images] int32 (-1 if a group exceeds
+ *     max_per_image); oks_top [N] float64 or NULL -- oks of every person against its image's
+ *     first pick (the pick's own entry is not written). */
+int udp_oks_nms(const float *preds, const double *area, const double *score, const int32_t *img_off,
+                int num_images, int max_per_image, int K, double thresh, const double *sigmas_host,
+                int use_vis_thre, double in_vis_thre, int soft, int max_dets, int32_t *keep,
+                int32_t *keep_cnt, double *oks_top, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

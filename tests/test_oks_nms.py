@@ -38,3 +38,56 @@ def test_oracle_direct_nms_matches_reference(case):
     p, area, score, sig = G.direct_inputs(case)
     keep = (O.soft_oks_nms if soft else O.oks_nms)(p, area, score, thresh, sig, vis)
     assert keep == GOLD[case + "_keep"].tolist()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(G.CASES))
+def test_device_rescore_nms_matches_reference(case):
+    from udp_pose_b200 import reference_api as R
+    p, b, img = G.inputs(case)
+    _check(case, *R.coco_rescore_nms(p, b, img, G.IN_VIS_THRE, G.OKS_THRE, soft_nms=G.CASES[case][4]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(G.DIRECT))
+def test_device_direct_nms_matches_reference(case):
+    """The reference's own signatures: oks_nms / soft_oks_nms(kpts_db, thresh, sigmas, in_vis_thre)."""
+    from udp_pose_b200 import reference_api as R
+    soft, thresh, vis, _ = G.DIRECT[case]
+    p, area, score, sig = G.direct_inputs(case)
+    db = [{"keypoints": p[i], "area": area[i], "score": score[i]} for i in range(len(p))]
+    keep = (R.soft_oks_nms if soft else R.oks_nms)(db, thresh, sig, vis)
+    assert list(keep) == GOLD[case + "_keep"].tolist()
+    assert R.oks_nms([], 0.9) == [] and list(R.soft_oks_nms([], 0.9)) == []
+
+
+@pytest.mark.gpu
+def test_device_oks_values_and_large_batch():
+    """512 images x up to 64 persons (16 489 in all) against the oracle: kept rows exact; the OKS of every person
+    against its image's top pick within 4 ulp of the numpy value (CUDA exp vs numpy exp)."""
+    import torch
+    from udp_pose_b200 import device_api as D, reference_api as R, synth
+    preds, boxes, img = synth.nms_persons(512, 64, 17, np.random.default_rng(3))
+    score, kept = R.coco_rescore_nms(preds, boxes, img, 0.2, 0.9)
+    o_score, o_kept = O.coco_rescore_nms(preds, boxes, img, 0.2, 0.9)
+    assert np.array_equal(score, o_score) and kept == o_kept
+    s_score, s_kept = R.coco_rescore_nms(preds, boxes, img, 0.2, 0.9, soft_nms=True)
+    assert s_kept == O.coco_rescore_nms(preds, boxes, img, 0.2, 0.9, soft=True)[1]
+    # one image, OKS values
+    rows = np.nonzero(img == img[0])[0]
+    r = D.oks_nms_batch(preds[rows], boxes[rows, 4], o_score[rows], np.array([0, len(rows)], np.int32), len(rows), 0.9,
+                        want_oks=True)
+    top = int(r["keep"][0])
+    rest = [j for j in range(len(rows)) if j != top]
+    want = O.oks_row(preds[rows], boxes[rows, 4], top, rest)
+    got = r["oks_top"].cpu().numpy()[rest]
+    assert np.all(np.abs(got - want) <= 4 * np.spacing(want))
+    assert np.isnan(r["oks_top"].cpu().numpy()[top])
+
+
+@pytest.mark.gpu
+def test_device_nms_rejects_oversized_image():
+    from udp_pose_b200 import device_api as D, synth
+    preds, boxes, img = synth.nms_persons(1, 8, 17, np.random.default_rng(4), exact=True)
+    r = D.oks_nms_batch(preds, boxes[:, 4], boxes[:, 5], np.array([0, 8], np.int32), 4, 0.9)
+    assert int(r["keep_cnt"][0]) == -1

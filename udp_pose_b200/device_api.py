@@ -371,3 +371,40 @@ def accuracy_pck(output, target, ch_stride=1, thr=0.5):
     _lib.call("udp_accuracy_pck", _ptr(output), _ptr(target), int(ch_stride), K, int(w), int(h), N, float(thr),
               _ptr(pred), _ptr(dists), _ptr(acc), _ptr(avg), _ptr(cnt), _stream())
     return dict(acc=acc, avg_acc=avg, cnt=cnt, pred=pred, dists=dists)
+
+
+def coco_rescore(preds, box_score, in_vis_thre):
+    """the rescoring of lib/dataset/coco.py:326-339.  preds f32 CUDA [N,K,3]
+    (x, y, maxval), box_score f64 [N] -> score f64 CUDA [N]."""
+    preds, box_score = _dev(preds, _F32), _dev(box_score, _F64)
+    N, K, _ = preds.shape
+    score = torch.empty((N,), dtype=_F64, device=preds.device)
+    _lib.call("udp_coco_rescore", _ptr(preds), _ptr(box_score), int(K), int(N), float(in_vis_thre), _ptr(score), _stream())
+    return score
+
+
+def oks_nms_batch(preds, area, score, img_off, max_per_image, thresh, soft=False, sigmas=None, in_vis_thre=None,
+                  max_dets=20, want_oks=False):
+    """oks_nms / soft_oks_nms of lib/nms/nms.py:97-180 for every image at once.
+    preds f32 [N,K,3], area/score f64 [N], img_off int32 [I+1] (persons of image i are rows
+    img_off[i]:img_off[i+1]); max_per_image is a host int (no device sync here).  sigmas: host
+    sequence of K floats (already /10) or None = COCO's.  Returns dict(keep i32 [N] -- image i's
+    kept global rows, in keep order, start at keep[img_off[i]] -- keep_cnt i32 [I], oks_top f64 [N]
+    or None); CUDA tensors, nothing synchronised."""
+    preds, area, score = _dev(preds, _F32), _dev(area, _F64), _dev(score, _F64)
+    img_off = _dev(img_off, torch.int32)
+    N, K, _ = preds.shape
+    I = img_off.numel() - 1
+    dev = preds.device
+    keep = torch.full((N,), -1, dtype=torch.int32, device=dev)
+    keep_cnt = torch.zeros((max(I, 0),), dtype=torch.int32, device=dev)
+    oks = torch.full((N,), float("nan"), dtype=_F64, device=dev) if want_oks else None
+    sig = None
+    if sigmas is not None:
+        sig = np.ascontiguousarray(sigmas, np.float64)
+        assert sig.shape == (K,)
+    _lib.call("udp_oks_nms", _ptr(preds), _ptr(area), _ptr(score), _ptr(img_off), int(I), int(max_per_image), int(K),
+              float(thresh), sig.ctypes.data_as(C.c_void_p) if sig is not None else None,
+              int(in_vis_thre is not None), float(in_vis_thre or 0.0), int(bool(soft)), int(max_dets),
+              _ptr(keep), _ptr(keep_cnt), _ptr(oks), _stream())
+    return dict(keep=keep, keep_cnt=keep_cnt, oks_top=oks)

@@ -389,6 +389,61 @@ def accuracy(output, target, hm_type='gaussian', thr=0.5):
     return acc, float(_np(r["avg_acc"])[0]) if int(_np(r["cnt"])[0]) else 0, int(_np(r["cnt"])[0]), _np(r["pred"])
 
 
+def _nms_one(kpts_db, thresh, sigmas, in_vis_thre, soft):
+    if len(kpts_db) == 0:
+        return []
+    preds = np.stack([np.asarray(k['keypoints'], np.float32).reshape(-1, 3) for k in kpts_db])
+    area = np.array([k['area'] for k in kpts_db], np.float64)
+    score = np.array([k['score'] for k in kpts_db], np.float64)
+    n = len(kpts_db)
+    r = D.oks_nms_batch(preds, area, score, np.array([0, n], np.int32), n, thresh, soft=soft,
+                        sigmas=sigmas if isinstance(sigmas, np.ndarray) else None, in_vis_thre=in_vis_thre)
+    cnt = int(_np(r["keep_cnt"])[0])
+    if cnt < 0:
+        raise D._lib.UdpCodecError("udp_oks_nms: image larger than max_per_image")
+    return _np(r["keep"])[:cnt].astype(np.intp)
+
+
+def oks_nms(kpts_db, thresh, sigmas=None, in_vis_thre=None):
+    """lib/nms/nms.py:97-124: kpts_db = list of dicts with 'keypoints' [K,3], 'area', 'score';
+    returns the kept indices in keep order ([] for an empty list; an index array otherwise, where the
+    reference builds a python list of the same numbers).  As in the reference, a `sigmas` that is not
+    an ndarray means COCO's defaults (:76-77)."""
+    r = _nms_one(kpts_db, thresh, sigmas, in_vis_thre, False)
+    return [int(i) for i in r]
+
+
+def soft_oks_nms(kpts_db, thresh, sigmas=None, in_vis_thre=None):
+    """lib/nms/nms.py:139-180: at most 20 kept indices (np.intp array, as the reference returns)."""
+    return _nms_one(kpts_db, thresh, sigmas, in_vis_thre, True)
+
+
+def coco_rescore_nms(preds, all_boxes, image_ids, in_vis_thre, oks_thre, soft_nms=False):
+    """The rescoring + NMS block of COCODataset.evaluate (lib/dataset/coco.py:308-356) for the whole
+    result set in two launches.  preds [N,K,3] (validate()'s all_preds), all_boxes [N,6]
+    (cx, cy, sx, sy, area, box score), image_ids [N] ints.  Persons are grouped by image in
+    first-appearance order, rows in input order (what the reference's defaultdict does, :317-319).
+    Returns (score f64 [N], list of kept row lists, one per image in that order)."""
+    preds = np.ascontiguousarray(preds, np.float32)
+    all_boxes = np.asarray(all_boxes, np.float64)
+    ids = np.asarray(image_ids)
+    _, first, inv = np.unique(ids, return_index=True, return_inverse=True)
+    rank = np.argsort(np.argsort(first))            # image -> position by first appearance
+    grp = rank[inv]
+    rows = np.argsort(grp, kind="stable")           # grouped row order
+    counts = np.bincount(grp, minlength=len(first))
+    off = np.zeros(len(first) + 1, np.int32)
+    off[1:] = np.cumsum(counts)
+    p = D._dev(preds[rows], torch.float32)
+    score = D.coco_rescore(p, all_boxes[rows, 5], in_vis_thre)
+    r = D.oks_nms_batch(p, all_boxes[rows, 4], score, off, int(counts.max()) if len(counts) else 0, oks_thre, soft=soft_nms)
+    keep, cnt, sc = _np(r["keep"]), _np(r["keep_cnt"]), _np(score)
+    out_score = np.empty(len(preds), np.float64)
+    out_score[rows] = sc
+    kept = [[int(rows[j]) for j in keep[off[i]:off[i] + cnt[i]]] for i in range(len(cnt))]
+    return out_score, kept
+
+
 def install(inference=None, transforms=None, joints_dataset=None, evaluate=None):
     """Substitute the CUDA codec into already-imported reference modules
     (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset, lib.core.evaluate).

@@ -129,3 +129,29 @@ def adversarial_heatmaps(cfg, rng):
         z[k, rng.integers(0, h), rng.integers(0, w)] = 0.9
     rows.append(z)
     return np.stack(rows).astype(np.float32)
+
+
+def nms_persons(images, max_per_image, K, rng, exact=False):
+    """Pose results for the COCO rescoring + OKS-NMS step, in the layout validate()
+    builds (lib/core/function.py:208-214): preds f32 [N,K,3] (x, y, maxval), all_boxes f64 [N,6]
+    (cx, cy, sx, sy, area, box score), image id int64 [N], rows shuffled across images.  Every image
+    has n ~ U{1..max_per_image} persons (exactly max_per_image with exact=True) drawn around n/4 base
+    poses with jitters from 0.5 % to 25 % of the body size, so near-duplicates (suppressed) and
+    distinct poses (kept) both occur."""
+    n_img = np.full(images, max_per_image) if exact else rng.integers(1, max_per_image + 1, images)
+    img = np.repeat(np.arange(images, dtype=np.int64), n_img)
+    N = len(img)
+    start = np.repeat(np.cumsum(n_img) - n_img, n_img)
+    nbase = np.maximum(1, np.repeat(n_img, n_img) // 4)
+    b = start + rng.integers(0, 1 << 30, N) % nbase                 # row that acts as this person's base pose
+    centre = rng.uniform(40, 600, (N, 1, 2))
+    shape = rng.normal(0, 40, (N, K, 2))
+    size = rng.uniform(60, 260, N)
+    jitter = rng.choice([0.5, 2.0, 6.0, 25.0], N) * size[b] / 100.0
+    xy = centre[b] + shape[b] + rng.normal(0, 1, (N, K, 2)) * jitter[:, None, None]
+    mv = rng.uniform(0.05, 1.0, (N, K, 1)) * (rng.uniform(size=(N, K, 1)) > 0.1)
+    preds = np.concatenate([xy, mv], 2).astype(np.float32)
+    s = np.stack([size[b] * 0.75, size[b]], 1) / 200.0 * rng.uniform(0.9, 1.1, (N, 1))
+    boxes = np.concatenate([xy.mean(1), s, np.prod(s * 200.0, 1, keepdims=True), rng.uniform(0.05, 1.0, (N, 1))], 1)
+    perm = rng.permutation(N)
+    return preds[perm], boxes[perm].astype(np.float64), img[perm]
