@@ -464,6 +464,34 @@ def run_ours(args):
             torch.cuda.synchronize()
             fused["accuracy_pck"] = {"ms": round(a.elapsed_time(b) / reps, 4), "bytes_per_person": 2.0 * K * h * w * 4 + 8 * K + 8 * K}
 
+    # ---- SURVEY 8(f)-3 (outside the timed step): COCO rescoring + OKS-NMS of B pose results, one CTA per image
+    nms = None
+    if world == 1 and not args.no_fused:
+        from udp_pose_b200 import synth as _synth
+        n_img = max(1, B // 16)
+        npreds, nboxes, nimg = _synth.nms_persons(n_img, 32, 17, np.random.default_rng(77))
+        order = np.argsort(nimg, kind="stable")
+        off = np.zeros(n_img + 1, np.int32)
+        off[1:] = np.cumsum(np.bincount(nimg, minlength=n_img))
+        dp = torch.from_numpy(npreds[order]).cuda()
+        da, db = torch.from_numpy(nboxes[order, 4].copy()).cuda(), torch.from_numpy(nboxes[order, 5].copy()).cuda()
+        doff = torch.from_numpy(off).cuda()
+        nms = {"persons": int(len(npreds)), "images": int(n_img)}
+        for key, soft in (("hard_ms", False), ("soft_ms", True)):
+            for _ in range(3):
+                r = D.oks_nms_batch(dp, da, D.coco_rescore(dp, db, 0.2), doff, 32, 0.9, soft=soft)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(10):
+                r = D.oks_nms_batch(dp, da, D.coco_rescore(dp, db, 0.2), doff, 32, 0.9, soft=soft)
+            b.record()
+            torch.cuda.synchronize()
+            nms[key] = round(a.elapsed_time(b) / 10, 4)
+            nms["kept_" + key[:4]] = int(r["keep_cnt"].sum())
+        nms["persons_per_s"] = round(nms["persons"] / (nms["hard_ms"] * 1e-3))
+        nms["note"] = ("udp_coco_rescore + udp_oks_nms (coco.py:321-356, nms.py:75-180), in_vis_thre 0.2, oks_thre 0.9, up to 32 persons "
+                       "per image; sequential greedy picks per image, float64 exp: latency/FP64-bound, 232 B per person, no HBM roofline")
+
     # ---- end to end through host buffers (pinned), H2D and D2H inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -575,9 +603,11 @@ def run_ours(args):
         for v in fused.values():
             v["achieved_gbs"] = round(v["bytes_per_person"] * B / (v["ms"] * 1e-3) / 1e9, 1)
             v["frac"] = round(v["achieved_gbs"] / peak, 4)
-        line["next"] = dict(fused, note="SURVEY 8(f) ranks 1-2, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
+        line["next"] = dict(fused, note="SURVEY 8(f) ranks 1-3, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
                                         "as float32 CHW (and the x-mirrored flip-test input) straight from the gather; udp_accuracy_pck is evaluate.py:accuracy "
                                         "on device tensors; not part of `value`")
+    if nms:
+        line.setdefault("next", {})["oks_nms"] = nms
     if e2e:
         line["e2e"] = e2e
     if not args.no_cpu and world == 1:

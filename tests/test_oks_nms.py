@@ -91,3 +91,15 @@ def test_device_nms_rejects_oversized_image():
     preds, boxes, img = synth.nms_persons(1, 8, 17, np.random.default_rng(4), exact=True)
     r = D.oks_nms_batch(preds, boxes[:, 4], boxes[:, 5], np.array([0, 8], np.int32), 4, 0.9)
     assert int(r["keep_cnt"][0]) == -1
+
+
+def test_install_rebinds_nms_names():
+    """install(nms=...) substitutes oks_nms / soft_oks_nms in the modules that hold the names
+    (lib/nms/nms.py and lib/dataset/coco.py, which imports them at :20); no GPU needed."""
+    import types
+    from udp_pose_b200 import reference_api as R
+    a, b = types.ModuleType("nms.nms"), types.ModuleType("dataset.coco")
+    a.oks_nms = a.soft_oks_nms = b.oks_nms = b.soft_oks_nms = None
+    saved = R.install(nms=[a, b])
+    assert a.oks_nms is R.oks_nms and b.soft_oks_nms is R.soft_oks_nms
+    assert ("nms.nms", "oks_nms") in saved and ("dataset.coco", "soft_oks_nms") in saved

@@ -444,9 +444,10 @@ def coco_rescore_nms(preds, all_boxes, image_ids, in_vis_thre, oks_thre, soft_nm
     return out_score, kept
 
 
-def install(inference=None, transforms=None, joints_dataset=None, evaluate=None):
+def install(inference=None, transforms=None, joints_dataset=None, evaluate=None, nms=None):
     """Substitute the CUDA codec into already-imported reference modules
-    (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset, lib.core.evaluate).
+    (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset, lib.core.evaluate, and
+    lib.nms.nms and/or lib.dataset.coco for oks_nms / soft_oks_nms -- `nms` may be a module or a list).
     Returns a dict {(module_name, attr): original} so the caller can undo it."""
     saved = {}
 
@@ -461,6 +462,9 @@ def install(inference=None, transforms=None, joints_dataset=None, evaluate=None)
     for nm in ("flip_back", "flip_back_offset", "fliplr_joints", "transform_preds"):
         put(transforms, nm, globals()[nm])
     put(evaluate, "accuracy", accuracy)
+    for mod in (nms if isinstance(nms, (list, tuple)) else [nms]):
+        put(mod, "oks_nms", oks_nms)
+        put(mod, "soft_oks_nms", soft_oks_nms)
     if joints_dataset is not None:
         put(joints_dataset, "get_warpmatrix", get_warpmatrix)
         put(joints_dataset, "rotate_points", rotate_points)
