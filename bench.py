@@ -354,6 +354,15 @@ def link_ceiling(torch, up_bytes, down_bytes, persons):
 STAGES = ["warp_matrices", "crop", "rotate_points", "encode", "decode"]
 
 
+def workload_text(cfg):
+    """One-line description of a step for the JSON line's config.workload."""
+    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+    enc = {"offset": "UDPv1 offset target (KPD %g)" % cfg.kpd, "gaussian": "UDP Gaussian target (sigma %g)" % cfg.sigma,
+           "rsn": "RSN 5-scale full-map target"}[cfg.target_type]
+    dec = "flip-test offset-vote decode" if cfg.target_type == "offset" else "flip-test DARK-refined decode"
+    return "crop %dx%d + %s + %s, %dx%dx%d maps" % (H, W, enc, dec, cfg.channels, h, w)
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -592,7 +601,7 @@ def run_ours(args):
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 maps / f64 joint prologue / u8 crop", "data": "synthetic",
-            "config": {"workload": cfg.name + ": crop 256x192 + UDPv1 offset target (KPD 3.5) + flip-test offset-vote decode, 51x64x48 maps",
+            "config": {"workload": cfg.name + ": " + workload_text(cfg),
                        "cfg": args.config, "persons_per_gpu_per_step": B, "sharding": "contiguous persons per rank, one all_gather of [B,K,3] keypoints per step",
                        "l2": "inputs larger than L2 (%.1f GB of network outputs per step per GPU; the %d source images, %.0f MB, are the SURVEY 8d pool)" % (2 * cfg.channels * h * w * 4 * B / 1e9, N_IMAGES, N_IMAGES * 480 * 640 * 3 / 1e6)},
             "roofline": roofline, "kernels": kern,
