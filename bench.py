@@ -583,6 +583,15 @@ def run_ours(args):
     kern["decode"]["survey_bytes_per_person"] = ab["decode_survey"]
     kern["decode"]["frac_on_survey_bytes"] = round(ab["decode_survey"] * B / (stage_ms["decode"] * 1e-3) / 1e9 / peak, 4)
     dom = max(STAGES, key=lambda n: stage_ms[n])
+    # the north star states its target per PATH: encode = warp + target (four kernels), decode = one kernel
+    enc_st = ["warp_matrices", "crop", "rotate_points", "encode"]
+    enc_ms, enc_b = sum(stage_ms[n] for n in enc_st), sum(ab[n] for n in enc_st)
+    paths = {"encode_path": {"stages": enc_st, "ms": round(enc_ms, 4), "bytes_per_person": round(enc_b, 1),
+                             "achieved_gbs": round(enc_b * B / (enc_ms * 1e-3) / 1e9, 1)},
+             "decode_path": {"stages": ["decode"], "ms": kern["decode"]["ms"], "bytes_per_person": kern["decode"]["bytes_per_person"],
+                             "achieved_gbs": kern["decode"]["achieved_gbs"]}}
+    for v in paths.values():
+        v["frac"] = round(v["achieved_gbs"] / peak, 4)
     # measured DRAM bytes of one launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, committed in
     # profiles/traffic.json for this config and batch; scaled linearly to another batch size)
     traffic = None
@@ -604,7 +613,7 @@ def run_ours(args):
             "config": {"workload": cfg.name + ": " + workload_text(cfg),
                        "cfg": args.config, "persons_per_gpu_per_step": B, "sharding": "contiguous persons per rank, one all_gather of [B,K,3] keypoints per step",
                        "l2": "inputs larger than L2 (%.1f GB of network outputs per step per GPU; the %d source images, %.0f MB, are the SURVEY 8d pool)" % (2 * cfg.channels * h * w * 4 * B / 1e9, N_IMAGES, N_IMAGES * 480 * 640 * 3 / 1e6)},
-            "roofline": roofline, "kernels": kern,
+            "roofline": roofline, "kernels": kern, "paths": paths,
             "gather_ms": round(stage_ms["gather"], 4),
             "gpu_launches": (len(STAGES) - 1 + D.crop_launches(cfg.image_size)) * args.steps,
             "clocks": clocks}

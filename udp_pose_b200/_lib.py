@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libudp_codec.so")
+# UDP_CODEC_LIB: another build of the same library (kernel tuning experiments); no fallback either way
+LIB_PATH = os.environ.get("UDP_CODEC_LIB") or os.path.join(HERE, "libudp_codec.so")
 
 _vp, _i, _d, _f = C.c_void_p, C.c_int, C.c_double, C.c_float
 

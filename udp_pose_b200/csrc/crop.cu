@@ -166,7 +166,10 @@ warp_affine_u8_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, cons
 // ---------------------------------------------------------------------------------------
 constexpr int CT = 32;                       // tile edge (output pixels)
 constexpr int CT_THREADS = 128;              // 4 warps, 8 tile rows each
-constexpr int CT_SMEM = 24 * 1024;           // footprint buffer (bytes), + 16 bytes slack
+#ifndef UDP_CROP_SMEM_KB
+#define UDP_CROP_SMEM_KB 24
+#endif
+constexpr int CT_SMEM = UDP_CROP_SMEM_KB * 1024;  // footprint buffer (bytes), + 16 bytes slack
 
 __device__ __forceinline__ void zero_bytes(uint8_t *base, int lo, int hi)
 {

@@ -95,6 +95,15 @@ class SourceImages:
         self.stride = torch.from_numpy(st).to(dev)
         self.n = len(index)
 
+    @classmethod
+    def from_tables(cls, images, ptrs, h, w, stride):
+        """Wrap per-person tables that are already on the device (ptrs int64 [N], h/w/stride int32
+        [N]); `images` is kept only to hold the storage alive.  Used by the host pipeline, which
+        uploads the pointer table with each chunk instead of building it per call."""
+        o = cls.__new__(cls)
+        o.images, o.ptrs, o.h, o.w, o.stride, o.n = images, ptrs, h, w, stride, int(ptrs.numel())
+        return o
+
 
 def crop_batch(src, M, image_size, out=None):
     """a2 cv2.warpAffine(img, M, (W,H), WARP_INVERSE_MAP|INTER_LINEAR) for N persons.

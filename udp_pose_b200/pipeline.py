@@ -47,7 +47,7 @@ class HostBatch:
     def h2d_bytes(self):
         t = [self.images, self.center, self.scale, self.rot, self.joints, self.joints_vis, self.out,
              self.out_flipped]
-        return int(sum(x.numel() * x.element_size() for x in t))
+        return int(sum(x.numel() * x.element_size() for x in t)) + 8 * self.n  # + the image pointer table
 
     def d2h_bytes(self):
         t = [self.crop, self.target, self.target_weight, self.keypoints]
@@ -81,10 +81,20 @@ class HostPipeline:
                 out=torch.empty((chunk, C, h, w), dtype=torch.float32, device=dev),
                 fl=torch.empty((chunk, C, h, w), dtype=torch.float32, device=dev),
                 crop=torch.empty((chunk, H, W, 3), dtype=torch.uint8, device=dev),
+                ptrs=torch.empty((chunk,), dtype=torch.int64, device=dev),
                 target=torch.empty((chunk, tc, h, w), dtype=torch.float32, device=dev),
                 up=torch.cuda.Event(), ran=torch.cuda.Event(), down=torch.cuda.Event(),
             )
         self.slots = [slot() for _ in range(max(2, n_slots))]
+        # per-person image tables: the pool is dense, so height / width / pitch are constants and
+        # only the pointer table travels (pinned, with each chunk's other inputs)
+        self.src_h = torch.full((chunk,), src_hw[0], dtype=torch.int32, device=dev)
+        self.src_w = torch.full((chunk,), src_hw[1], dtype=torch.int32, device=dev)
+        self.src_st = torch.full((chunk,), src_hw[1] * 3, dtype=torch.int32, device=dev)
+        self.img_bytes = src_hw[0] * src_hw[1] * 3
+        self.ptr_host = [None, None]          # two tables: run k+1 (sync=False) fills one while run k still uploads from the other
+        self.ptr_done = [torch.cuda.Event(), torch.cuda.Event()]
+        self.runs = 0
         self.chunks_done = 0
         self.launches = 0
 
@@ -119,6 +129,13 @@ class HostPipeline:
         enqueued (a following run() then overlaps its uploads with this one's downloads --
         call synchronize() before reading the host buffers)."""
         cfg, n, chunk = self.cfg, hb.n, self.chunk
+        par = self.runs & 1
+        self.runs += 1
+        self.ptr_done[par].synchronize()      # the run before last has finished uploading from this table
+        if self.ptr_host[par] is None or self.ptr_host[par].numel() < n:
+            self.ptr_host[par] = pinned((n,), torch.int64)
+        ptr_host = self.ptr_host[par]
+        np.add(self.images.data_ptr(), np.asarray(hb.image_index[:n], np.int64) * self.img_bytes, out=ptr_host.numpy()[:n])
         with torch.cuda.stream(self.s_up):
             self.s_up.wait_stream(self.s_run)  # kernels of an unsynchronised previous run still read the images
             self.images.copy_(hb.images, non_blocking=True)
@@ -132,10 +149,11 @@ class HostPipeline:
                                  ("joints", hb.joints), ("vis", hb.joints_vis), ("out", hb.out),
                                  ("fl", hb.out_flipped)):
                     sl[key][:m].copy_(src[sel], non_blocking=True)
+                sl["ptrs"][:m].copy_(ptr_host[sel], non_blocking=True)
                 sl["up"].record()
             with torch.cuda.stream(self.s_run):
                 self.s_run.wait_event(sl["up"])
-                src = D.SourceImages(self.images, hb.image_index[sel])
+                src = D.SourceImages.from_tables(self.images, sl["ptrs"][:m], self.src_h[:m], self.src_w[:m], self.src_st[:m])
                 M = D.warp_matrices(sl["center"][:m], sl["scale"][:m], sl["rot"][:m], cfg.image_size)
                 D.crop_batch(src, M, cfg.image_size, out=sl["crop"][:m])
                 j3 = D.rotate_points_batch(sl["joints"][:m], sl["rot"][:m], sl["center"][:m],
@@ -160,6 +178,7 @@ class HostPipeline:
                 # keep the temporaries alive until the download stream is done with them
                 tw.record_stream(self.s_down)
                 r["packed"].record_stream(self.s_down)
+        self.ptr_done[par].record(self.s_up)
         if sync:
             self.synchronize()
 
