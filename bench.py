@@ -228,18 +228,15 @@ def make_device_workload(cfg, B, rank, torch, D):
 # ----------------------------------------------------------------------------------------
 # CPU baseline: the numpy/cv2 port of the reference path on the host cores
 # ----------------------------------------------------------------------------------------
-def _cpu_worker(task):
-    """One worker = one core: the reference's per-person path on `n` persons (seeded)."""
-    cfg_id, seed, n = task
+def _cpu_inputs(cfg_id, seed, n):
+    """Seeded inputs of one worker (SURVEY 8d distributions); generated once, outside every timed region."""
     os.environ["OMP_NUM_THREADS"] = "1"
     import cv2
     cv2.setNumThreads(1)
-    from oracle import np_port as P
     from udp_pose_b200 import synth
     from udp_pose_b200.configs import CONFIGS
     cfg = CONFIGS[cfg_id]
     rng = np.random.default_rng(seed)
-    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
     c, s, r = synth.boxes(cfg, n, rng, rotate=True)
     imgs = synth.source_images(2, rng)
     K = cfg.num_joints
@@ -248,6 +245,14 @@ def _cpu_worker(task):
     js[..., 1] = c[:, None, 1] + rng.uniform(-0.6, 0.6, (n, K)) * s[:, None, 1] * 200.0
     vis = np.ones((n, K, 3))
     out, fl = synth.heatmaps(cfg, n, rng)
+    return dict(cfg=cfg, n=n, c=c, s=s, r=r, imgs=imgs, js=js, vis=vis, out=out, fl=fl)
+
+
+def _cpu_pass(st):
+    """One worker = one core: the reference's per-person path over the worker's persons; seconds."""
+    from oracle import np_port as P
+    cfg, n, c, s, r, imgs, js, vis = (st[k] for k in ("cfg", "n", "c", "s", "r", "imgs", "js", "vis"))
+    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
     trip = cfg.target_type == "offset"
     t0 = time.perf_counter()
     for i in range(n):  # encode: one person per __getitem__ call
@@ -263,60 +268,113 @@ def _cpu_worker(task):
     bs = 32  # decode: per validation batch, as validate() does
     with np.errstate(all="ignore"):
         for lo in range(0, n, bs):
-            avg = P.unflip_average(out[lo:lo + bs], fl[lo:lo + bs], cfg.flip_pairs, trip)
+            avg = P.unflip_average(st["out"][lo:lo + bs], st["fl"][lo:lo + bs], cfg.flip_pairs, trip)
             P.final_preds(avg, c[lo:lo + bs], s[lo:lo + bs], "offset" if trip else "gaussian",
                           cfg.kpd, cfg.post_process, cfg.pre_div)
-    return n, time.perf_counter() - t0
+    return time.perf_counter() - t0
 
 
-def cpu_baseline(cfg_id, seconds, per_worker=None):
-    """persons/s of the CPU port on all host cores (one single-threaded process per core)."""
-    import multiprocessing as mp
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    ctx = mp.get_context("spawn")
-    with ctx.Pool(cores) as pool:
-        if per_worker is None:
-            n0, t = pool.apply(_cpu_worker, ((cfg_id, 1, 8),))  # calibrate on one core
-            per_worker = max(8, min(512, int(seconds * 0.6 * n0 / t)))
-        t0 = time.perf_counter()
-        res = pool.map(_cpu_worker, [(cfg_id, 100 + i, per_worker) for i in range(cores)])
-        wall = time.perf_counter() - t0
-    n = sum(a for a, _ in res)
-    core_rate = float(np.mean([a / b for a, b in res]))
-    busy = max(b for _, b in res)  # slowest worker's timed region (input generation excluded)
-    return {"value": n / busy, "unit": UNIT, "cores": cores, "kind": "port",
-            "per_core": core_rate, "per_worker": per_worker,
-            "sample": "%d persons (%d per core x %d single-threaded processes) of the same cfg-%d "
+def _cpu_worker_main(conn, cfg_id, seed, n):
+    st = _cpu_inputs(cfg_id, seed, n)
+    conn.send("ready")
+    while conn.recv() is not None:
+        conn.send(_cpu_pass(st))
+
+
+class CpuArm:
+    """The CPU port on all host cores: one single-threaded process per core (the reference's
+    DataLoader-worker model, tools/train.py:145-151), each holding its own `per_worker` persons.
+    step() = every worker runs the encode+decode pass over its persons once; returns the slowest
+    worker's seconds."""
+
+    def __init__(self, cfg_id, per_worker):
+        import multiprocessing as mp
+        self.cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        self.per_worker = per_worker
+        ctx = mp.get_context("spawn")
+        self.w = []
+        for i in range(self.cores):
+            a, b = ctx.Pipe()
+            pr = ctx.Process(target=_cpu_worker_main, args=(b, cfg_id, 100 + i, per_worker), daemon=True)
+            pr.start()
+            self.w.append((pr, a))
+        for _, a in self.w:
+            a.recv()
+
+    def step(self):
+        for _, a in self.w:
+            a.send(1)
+        return [a.recv() for _, a in self.w]
+
+    def close(self):
+        for pr, a in self.w:
+            a.send(None)
+        for pr, _ in self.w:
+            pr.join(5)
+
+
+def _cpu_calibrate(cfg_id):
+    """persons/s of one core, from 8 persons run in this process."""
+    st = _cpu_inputs(cfg_id, 1, 8)
+    return 8 / _cpu_pass(st)
+
+
+def _cpu_record(cfg_id, arm, times):
+    """times: list (steps) of lists (workers) of seconds."""
+    n = arm.per_worker * arm.cores
+    busy = [max(t) for t in times]
+    rate = n * len(times) / sum(busy)
+    core_rate = float(np.mean([arm.per_worker / x for t in times for x in t]))
+    return {"value": rate, "unit": UNIT, "cores": arm.cores, "kind": "port",
+            "per_core": core_rate, "per_worker": arm.per_worker,
+            "sample": "%d step(s) of %d persons (%d per core x %d single-threaded processes) of the same cfg-%d "
                       "encode+decode pass with oracle/np_port.py (numpy+cv2 restatement of the "
                       "reference, checked against its golden vectors); value = persons / slowest worker's "
-                      "timed region (%.1f s); wall %.1f s incl. input generation"
-                      % (n, per_worker, cores, cfg_id, busy, wall)}
+                      "timed pass (%.2f s per step), inputs generated once per worker outside the timing"
+                      % (len(times), n, arm.per_worker, arm.cores, cfg_id, float(np.mean(busy)))}
+
+
+def cpu_baseline(cfg_id, seconds):
+    """persons/s of the CPU port on all host cores: one warm-up pass, one timed pass of about `seconds`."""
+    per_worker = max(8, min(512, int(seconds * 0.6 * _cpu_calibrate(cfg_id))))
+    arm = CpuArm(cfg_id, per_worker)
+    try:
+        arm.step()
+        return _cpu_record(cfg_id, arm, [arm.step()])
+    finally:
+        arm.close()
 
 
 def run_reference(args):
     """--impl reference: the reference's CPU path (numpy/cv2 port; the Python tree itself cannot
-    travel to the GPU box) on all host cores.  Rank 0 only."""
+    travel to the GPU box) on all host cores.  Rank 0 only.  Exactly --warmup untimed and --steps
+    timed steps; a step is one pass of every core over its own bounded sample, sized so that the
+    whole run takes about two minutes."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     from udp_pose_b200.configs import CONFIGS
     cfg = CONFIGS[args.config]
-    steps = max(1, min(args.steps, 3))
-    vals = []
-    per = None
-    for i in range(min(args.warmup, 1) + steps):
-        r = cpu_baseline(args.config, args.cpu_seconds, per)
-        per = r["per_worker"]
-        if i >= min(args.warmup, 1):
-            vals.append(r)
-    v = float(np.mean([x["value"] for x in vals]))
-    n_step = per * vals[0]["cores"]
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    per_worker = max(8, min(512, int(120.0 / (steps + warm) * _cpu_calibrate(args.config))))
+    arm = CpuArm(args.config, per_worker)
+    try:
+        for _ in range(warm):
+            arm.step()
+        t0 = time.perf_counter()
+        times = [arm.step() for _ in range(steps)]
+        wall = time.perf_counter() - t0
+    finally:
+        arm.close()
+    rec = _cpu_record(args.config, arm, times)
+    v = rec["value"]
+    n_step = per_worker * arm.cores
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * n_step / v,
+            "steps": steps, "warmup": warm, "ms_per_step": 1e3 * n_step / v, "wall_ms_per_step": 1e3 * wall / steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64/u8",
             "data": "synthetic",
-            "config": {"workload": cfg.name + " encode(crop+target)+decode(flip+vote)", "cfg": args.config,
+            "config": {"workload": cfg.name + ": " + workload_text(cfg) + " (CPU: numpy/cv2 port of the reference path)", "cfg": args.config,
                        "persons_per_step": n_step, "note": "CPU arm does not scale with --gpus"},
-            "cpu_baseline": dict(vals[-1], value=v),
+            "cpu_baseline": rec,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))

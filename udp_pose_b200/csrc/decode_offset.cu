@@ -388,7 +388,11 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
             UDP_LAUNCH_CHECK();                                                                  \
             return 0;                                                                            \
         } while (0);
-        UDP_OFF_PIPE(48, 64, 96, 4)
+#ifndef UDP_OFF_NT
+#define UDP_OFF_NT 96
+#define UDP_OFF_MINB 4
+#endif
+        UDP_OFF_PIPE(48, 64, UDP_OFF_NT, UDP_OFF_MINB)
         UDP_OFF_PIPE(64, 64, 128, 3)
         UDP_OFF_PIPE(72, 96, 288, 2)
 #undef UDP_OFF_PIPE
