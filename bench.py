@@ -531,6 +531,19 @@ def run_ours(args):
             torch.cuda.synchronize()
             fused["accuracy_pck"] = {"ms": round(a.elapsed_time(b) / reps, 4), "bytes_per_person": 2.0 * K * h * w * 4 + 8 * K + 8 * K}
 
+    if fused is not None:  # SURVEY 8(f)-4 (first half): the demo engines' quarter-offset decoder over the same network output
+        qb = torch.cat([wl["center"].float(), wl["scale"].float()], 1).contiguous()
+        for _ in range(3):
+            D.decode_quarter(wl["out"], qb)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            D.decode_quarter(wl["out"], qb)
+        b.record()
+        torch.cuda.synchronize()
+        fused["decode_quarter"] = {"ms": round(a.elapsed_time(b) / reps, 4), "bytes_per_person": cfg.channels * h * w * 4.0 + 16 + 8 * cfg.channels,
+                                   "maps_per_person": cfg.channels}
+
     # ---- SURVEY 8(f)-3 (outside the timed step): COCO rescoring + OKS-NMS of B pose results, one CTA per image
     nms = None
     if world == 1 and not args.no_fused:
@@ -681,7 +694,8 @@ def run_ours(args):
             v["frac"] = round(v["achieved_gbs"] / peak, 4)
         line["next"] = dict(fused, note="SURVEY 8(f) ranks 1-3, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
                                         "as float32 CHW (and the x-mirrored flip-test input) straight from the gather; udp_accuracy_pck is evaluate.py:accuracy "
-                                        "on device tensors; not part of `value`")
+                                        "on device tensors; udp_decode_quarter is tools/infer_utils/decode.py:get_final_preds over every channel of the same output; "
+                                        "oks_nms is coco.py:321-356; none is part of `value`")
     if nms:
         line.setdefault("next", {})["oks_nms"] = nms
     if e2e:

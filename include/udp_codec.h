@@ -160,6 +160,17 @@ int udp_accuracy_pck(const float *output, const float *target, int ch_stride, in
                      int N, double thr, float *pred, double *dists, double *acc, double *avg_acc,
                      int32_t *cnt, void *stream);
 
+/* SURVEY 8(f)-4 (first half)  the demo engines' quarter-offset decoder:
+ *     get_final_preds(heatmaps, boxes) of deep_hrnet/tools/infer_utils/decode.py:19-40, with its
+ *     get_max_preds (:43-52, coordinates -1 where maxval <= 0) and the biased transform_preds
+ *     (:55-62, scale*200/output_size).  heatmaps [N,K,h,w] float32; boxes [N,4] = (cx, cy, sx, sy),
+ *     float32 (boxes_f64 = 0) or float64 (1): the dtype selects the affine's arithmetic, as numpy
+ *     promotion does in the reference.  coords [N,K,2] int32 = the reference's `.astype(int)`
+ *     (INT32_MIN where numpy yields INT64_MIN: NaN or beyond int32); coords_f32 [N,K,2] (the values
+ *     before truncation) and maxvals [N,K] are optional (NULL). */
+int udp_decode_quarter(const float *heatmaps, const void *boxes, int boxes_f64, int K, int w, int h, int N,
+                       int32_t *coords, float *coords_f32, float *maxvals, void *stream);
+
 /* SURVEY 8(f)-3  COCO rescoring: deep_hrnet/lib/dataset/coco.py:326-339.
  *     preds [N,K,3] float32 (x, y, maxval -- the rows of validate()'s all_preds, function.py:208-209),
  *     box_score [N] float64 (all_boxes[:,5]).  score[n] = mean(maxval > in_vis_thre) * box_score[n]

@@ -98,6 +98,38 @@ def accuracy_pck(output, target, thr=0.5):
     return acc, avg, cnt, pred
 
 
+def decode_quarter(heatmaps, boxes):
+    """SURVEY 8(f)-4 (first half): the demo engines' quarter-offset decoder,
+    deep_hrnet/tools/infer_utils/decode.py:19-40 with its get_max_preds (:43-52: coordinates -1 where
+    maxval <= 0) and the biased transform_preds (:55-62: scale/output_size, not size-1).  Restated
+    with array operations in the dtypes the reference's scalars produce: float32 coordinates, +-0.25
+    where both neighbours exist (1 < px < W-1 and 1 < py < H-1), float32 affine for float32 boxes
+    (float64 products rounded into the float32 result for float64 boxes), truncation to int64.
+    heatmaps f32 [B,C,H,W], boxes [B,4] = (cx, cy, sx, sy) -> int64 [B,C,2]."""
+    hm = np.asarray(heatmaps, np.float32)
+    boxes = np.asarray(boxes)
+    B, C, H, W = hm.shape
+    flat = hm.reshape(B, C, -1)
+    idx = np.argmax(flat, 2)
+    mv = np.take_along_axis(flat, idx[..., None], 2)[..., 0]
+    coords = np.stack([idx % W, idx // W], -1).astype(np.float32)
+    coords = np.where((mv > 0.0)[..., None], coords, np.float32(-1))
+    px = np.floor(coords[..., 0] + np.float32(0.5)).astype(np.int64)
+    py = np.floor(coords[..., 1] + np.float32(0.5)).astype(np.int64)
+    inner = (1 < px) & (px < W - 1) & (1 < py) & (py < H - 1)
+    cx, cy = np.clip(px, 1, W - 2), np.clip(py, 1, H - 2)
+    b, c = np.meshgrid(np.arange(B), np.arange(C), indexing="ij")
+    dx = hm[b, c, cy, cx + 1] - hm[b, c, cy, cx - 1]
+    dy = hm[b, c, cy + 1, cx] - hm[b, c, cy - 1, cx]
+    shift = np.stack([np.sign(dx), np.sign(dy)], -1) * np.float32(0.25)
+    coords = np.where(inner[..., None], coords + shift, coords).astype(np.float32)
+    center, scale = boxes[:, None, :2], boxes[:, None, 2:] * 200          # boxes' dtype
+    per_px = scale / np.array([W, H])                                     # python ints: dtype kept
+    out = np.ones_like(coords)
+    out[...] = coords * per_px + center - scale * 0.5                     # float32 store (rounds a float64 result)
+    return out.astype(np.int64)
+
+
 COCO_SIGMAS = np.array([.26, .25, .25, .35, .35, .79, .79, .72, .72, .62, .62, 1.07, 1.07, .87, .87, .89, .89]) / 10.0
 
 

@@ -113,6 +113,59 @@ __global__ void pck_acc_kernel(const double *__restrict__ dists, int K, int N, d
     }
 }
 
+// SURVEY 8(f)-4 (first half): the demo engines' quarter-offset decoder,
+// deep_hrnet/tools/infer_utils/decode.py:19-40 (get_max_preds :43-52, biased transform_preds :55-62).
+// One CTA per map: the same streaming arg-max as above, then thread 0 reads the four neighbours
+// (L2 hits: the map was just streamed) and applies sign(diff) * 0.25, the scale/output_size
+// affine in the boxes' dtype and the truncation of `.astype(int)`.
+template <bool F64>
+__global__ void __launch_bounds__(PCK_THREADS)
+decode_quarter_kernel(const float *__restrict__ hm, const void *__restrict__ boxes, int K, int w, int h,
+                      int32_t *__restrict__ out, float *__restrict__ coords_f32, float *__restrict__ maxvals)
+{
+    __shared__ float red_v[32];
+    __shared__ int red_i[32];
+    const int hw = h * w;
+    const long long m = blockIdx.x;
+    const int n = (int)(m / K);
+    const float *map = hm + m * hw;
+    float v;
+    int idx;
+    pck_scan(map, hw, v, idx);
+    block_argmax(v, idx, red_v, red_i);
+    if (threadIdx.x != 0) return;
+    const bool pos = v > 0.0f;
+    const int px = pos ? idx % w : -1, py = pos ? idx / w : -1;
+    float cx = (float)px, cy = (float)py;
+    if (1 < px && px < w - 1 && 1 < py && py < h - 1) {
+        const float dx = __fsub_rn(map[py * w + px + 1], map[py * w + px - 1]);
+        const float dy = __fsub_rn(map[(py + 1) * w + px], map[(py - 1) * w + px]);
+        // np.sign: -1, 0, +1, NaN for NaN
+        const float sx = dx > 0.0f ? 1.0f : (dx < 0.0f ? -1.0f : (dx == 0.0f ? 0.0f : dx));
+        const float sy = dy > 0.0f ? 1.0f : (dy < 0.0f ? -1.0f : (dy == 0.0f ? 0.0f : dy));
+        cx = __fadd_rn(cx, __fmul_rn(sx, 0.25f));
+        cy = __fadd_rn(cy, __fmul_rn(sy, 0.25f));
+    }
+    float tx, ty;
+    if (F64) {
+        const double *b = reinterpret_cast<const double *>(boxes) + 4 * (long long)n;
+        const double s0 = __dmul_rn(b[2], 200.0), s1 = __dmul_rn(b[3], 200.0);
+        tx = (float)__dsub_rn(__dadd_rn(__dmul_rn((double)cx, __ddiv_rn(s0, (double)w)), b[0]), __dmul_rn(s0, 0.5));
+        ty = (float)__dsub_rn(__dadd_rn(__dmul_rn((double)cy, __ddiv_rn(s1, (double)h)), b[1]), __dmul_rn(s1, 0.5));
+    } else {
+        const float *b = reinterpret_cast<const float *>(boxes) + 4 * (long long)n;
+        const float s0 = __fmul_rn(b[2], 200.0f), s1 = __fmul_rn(b[3], 200.0f);
+        tx = __fsub_rn(__fadd_rn(__fmul_rn(cx, __fdiv_rn(s0, (float)w)), b[0]), __fmul_rn(s0, 0.5f));
+        ty = __fsub_rn(__fadd_rn(__fmul_rn(cy, __fdiv_rn(s1, (float)h)), b[1]), __fmul_rn(s1, 0.5f));
+    }
+    // .astype(int): truncation; NaN / out of int32 range -> INT32_MIN (numpy gives INT64_MIN there)
+    const bool okx = fabsf(tx) < 2147483520.0f, oky = fabsf(ty) < 2147483520.0f;
+    out[2 * m] = okx ? (int32_t)tx : INT32_MIN;
+    out[2 * m + 1] = oky ? (int32_t)ty : INT32_MIN;
+    if (coords_f32) { coords_f32[2 * m] = tx; coords_f32[2 * m + 1] = ty; }
+    if (maxvals) maxvals[m] = v;
+}
+
 }  // namespace udp
 
 extern "C" int udp_accuracy_pck(const float *output, const float *target, int ch_stride, int K, int w, int h,
@@ -131,6 +184,25 @@ extern "C" int udp_accuracy_pck(const float *output, const float *target, int ch
         UDP_LAUNCH_CHECK();
     }
     udp::pck_acc_kernel<<<1, 32 * K, 0, (cudaStream_t)stream>>>(dists, K, N, thr, acc, avg_acc, cnt);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int udp_decode_quarter(const float *heatmaps, const void *boxes, int boxes_f64, int K, int w, int h, int N,
+                                  int32_t *coords, float *coords_f32, float *maxvals, void *stream)
+{
+    if (N < 0 || K < 1 || w < 4 || h < 4 || ((w * h) & 3)) return UDP_EINVAL;
+    if (N == 0) return 0;
+    if (!heatmaps || !boxes || !coords) return UDP_EINVAL;
+    if (((uintptr_t)heatmaps & 15) != 0) return UDP_EINVAL;  // 16-byte vector loads
+    const long long maps = (long long)N * K;
+    if (maps > 0x7fffffffLL) return UDP_EINVAL;
+    if (boxes_f64)
+        udp::decode_quarter_kernel<true><<<(unsigned)maps, udp::PCK_THREADS, 0, (cudaStream_t)stream>>>(heatmaps, boxes, K, w, h, coords,
+                                                                                                 coords_f32, maxvals);
+    else
+        udp::decode_quarter_kernel<false><<<(unsigned)maps, udp::PCK_THREADS, 0, (cudaStream_t)stream>>>(heatmaps, boxes, K, w, h, coords,
+                                                                                                  coords_f32, maxvals);
     UDP_LAUNCH_CHECK();
     return 0;
 }

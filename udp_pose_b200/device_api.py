@@ -417,3 +417,23 @@ def oks_nms_batch(preds, area, score, img_off, max_per_image, thresh, soft=False
               int(in_vis_thre is not None), float(in_vis_thre or 0.0), int(bool(soft)), int(max_dets),
               _ptr(keep), _ptr(keep_cnt), _ptr(oks), _stream())
     return dict(keep=keep, keep_cnt=keep_cnt, oks_top=oks)
+
+
+def decode_quarter(heatmaps, boxes, want_float=False):
+    """SURVEY 8(f)-4 (first half): get_final_preds of tools/infer_utils/decode.py:19-40 (arg-max,
+    +-0.25 towards the higher neighbour, scale/output_size affine, truncation).  heatmaps f32 CUDA
+    [N,K,h,w]; boxes [N,4] (cx, cy, sx, sy) float32 or float64 (dtype kept: it selects the arithmetic).
+    Returns int32 CUDA [N,K,2] (and the float32 values before truncation, and maxvals [N,K])."""
+    heatmaps = _dev(heatmaps, _F32)
+    boxes = _dev(boxes)
+    if boxes.dtype not in (_F32, _F64):
+        boxes = boxes.to(_F32)
+    N, K, h, w = heatmaps.shape
+    assert boxes.shape == (N, 4)
+    dev = heatmaps.device
+    out = torch.empty((N, K, 2), dtype=torch.int32, device=dev)
+    cf = torch.empty((N, K, 2), dtype=_F32, device=dev) if want_float else None
+    mv = torch.empty((N, K), dtype=_F32, device=dev) if want_float else None
+    _lib.call("udp_decode_quarter", _ptr(heatmaps), _ptr(boxes), int(boxes.dtype == _F64), int(K), int(w), int(h), int(N),
+              _ptr(out), _ptr(cf), _ptr(mv), _stream())
+    return (out, cf, mv) if want_float else out

@@ -389,6 +389,18 @@ def accuracy(output, target, hm_type='gaussian', thr=0.5):
     return acc, float(_np(r["avg_acc"])[0]) if int(_np(r["cnt"])[0]) else 0, int(_np(r["cnt"])[0]), _np(r["pred"])
 
 
+def demo_get_final_preds(heatmaps, boxes):
+    """tools/infer_utils/decode.py:19-40 `get_final_preds(heatmaps: Tensor, boxes: Tensor)` -- the
+    quarter-offset decoder of the demo engines (named demo_* here because lib/core/inference.py owns
+    the name get_final_preds).  heatmaps [B,C,H,W] and boxes [B,4] = (cx, cy, sx, sy): torch tensors
+    (CPU or CUDA) or numpy arrays; returns int64 numpy [B,C,2] as the reference does."""
+    hm = heatmaps if isinstance(heatmaps, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(heatmaps, np.float32))
+    bx = boxes if isinstance(boxes, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(boxes))
+    out = _np(D.decode_quarter(hm.float(), bx)).astype(np.int64)
+    out[out == np.iinfo(np.int32).min] = np.iinfo(np.int64).min
+    return out
+
+
 def _nms_one(kpts_db, thresh, sigmas, in_vis_thre, soft):
     if len(kpts_db) == 0:
         return []
