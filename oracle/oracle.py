@@ -130,6 +130,71 @@ def decode_quarter(heatmaps, boxes):
     return out.astype(np.int64)
 
 
+# cv2.getGaussianKernel(n, 0, cv2.CV_64F)[: n // 2 + 1] as produced by OpenCV 4.13 (hex floats; the 5/7/9
+# tables are its fixed small kernels, 11/13/15 come from its bit-exact exp)
+GAUSS_F64 = {
+    5: ['0x1.0000000000000p-4', '0x1.0000000000000p-2', '0x1.8000000000000p-2'],
+    7: ['0x1.0000000000000p-5', '0x1.c000000000000p-4', '0x1.c000000000000p-3', '0x1.2000000000000p-2'],
+    9: ['0x1.0000000000000p-6', '0x1.a000000000000p-5', '0x1.e000000000000p-4', '0x1.9800000000000p-3', '0x1.e000000000000p-3'],
+    11: ['0x1.20c2564ee6772p-7', '0x1.bcb86a082c301p-6', '0x1.0ab50979aaf94p-4', '0x1.f2464c62edaf4p-4', '0x1.6a7e1d504a91dp-3',
+         '0x1.9ac20a36ea596p-3'],
+    13: ['0x1.7c090614dc85bp-8', '0x1.0cb82167c249dp-6', '0x1.3a8fe850a8f47p-5', '0x1.30cd237f01688p-4', '0x1.e8f1e9d4d4f8bp-4',
+         '0x1.449ed5bf3520ap-3', '0x1.64ccba4a2c88fp-3'],
+    15: ['0x1.0d2c46a814066p-8', '0x1.600a4b3638a7bp-7', '0x1.8d1b96696e28fp-6', '0x1.825954ed343f3p-5', '0x1.4431ed85d4175p-4',
+         '0x1.d543dae40f820p-4', '0x1.24ec9c4a6087bp-3', '0x1.3b69611f1d587p-3'],
+}
+
+
+def gauss_kernel_f64(n):
+    half = [float.fromhex(v) for v in GAUSS_F64[n]]
+    return np.array(half + half[-2::-1])
+
+
+def gaussian_blur_f64(a, n):
+    """cv2.GaussianBlur(a float64 [h,w], (n,n), 0), restated (udp_o_gaussian_blur_f64)."""
+    a = np.ascontiguousarray(a, np.float64)
+    out = np.empty_like(a)
+    k = gauss_kernel_f64(n)
+    lib().udp_o_gaussian_blur_f64(_p(a), _p(out), C.c_int(a.shape[0]), C.c_int(a.shape[1]), C.c_int(n), _p(k))
+    return out
+
+
+def rsn_get_results(outputs, centers, scales, in_shape, kernel=11, shift=0.25, border=10):
+    """SURVEY 8(f)-4 (second half): get_results of RSN/exps/RSN18.coco/test.py:25-71 (same function in the
+    Res18 / 4XRSN18 / RSN18.mpii experiments).  Per map: zero-padded float64 copy (border 10), Gaussian
+    blur, first arg-max, that element zeroed, second arg-max, a `shift`-pixel step from the first towards
+    the second, clamp, `x*4+2`, score = (out/255 + 0.5) at the rounded position (float32), then the
+    biased affine `kps / input * scale*200 + center - scale*200*0.5`.  Arrays restated per map with the
+    scalar types the reference's expressions produce; does not mutate `scales` (the reference does,
+    :26).  outputs f32 [N,K,h,w], centers/scales f32 [N,2], in_shape (H, W).
+    Returns (preds f64 [N,K,2], maxvals f64 [N,K,1])."""
+    outputs = np.asarray(outputs, np.float32)
+    N, K, h, w = outputs.shape
+    sc = np.asarray(scales, np.float32) * 200            # float32, as `scales *= 200` on the loader's array
+    ce = np.asarray(centers, np.float32)
+    preds, maxvals = np.zeros((N, K, 2)), np.zeros((N, K, 1))
+    for i in range(N):
+        score_map = outputs[i] / 255 + 0.5               # float32
+        for j in range(K):
+            dr = np.zeros((h + 2 * border, w + 2 * border))
+            dr[border:-border, border:-border] = outputs[i, j]
+            dr = gaussian_blur_f64(dr, kernel)
+            y, x = np.unravel_index(dr.argmax(), dr.shape)
+            dr[y, x] = 0
+            x, y = x - border, y - border
+            py, px = np.unravel_index(dr.argmax(), dr.shape)
+            px, py = px - (border + x), py - (border + y)
+            ln = (px ** 2 + py ** 2) ** 0.5
+            if ln > 1e-3:
+                x, y = x + shift * px / ln, y + shift * py / ln
+            x, y = max(0, min(x, w - 1)), max(0, min(y, h - 1))
+            preds[i, j] = x * 4 + 2, y * 4 + 2
+            maxvals[i, j, 0] = score_map[j, int(round(y) + 1e-9), int(round(x) + 1e-9)]
+        preds[i, :, 0] = preds[i, :, 0] / in_shape[1] * sc[i][0] + ce[i][0] - sc[i][0] * 0.5
+        preds[i, :, 1] = preds[i, :, 1] / in_shape[0] * sc[i][1] + ce[i][1] - sc[i][1] * 0.5
+    return preds, maxvals
+
+
 COCO_SIGMAS = np.array([.26, .25, .25, .35, .35, .79, .79, .72, .72, .62, .62, 1.07, 1.07, .87, .87, .89, .89]) / 10.0
 
 

@@ -269,3 +269,36 @@ void udp_o_decode_offset(const float *out, int K, int w, int h, double kpd, cons
     free(ox);
     free(oy);
 }
+
+/* ---------------------------------------------------------------------------------------
+ * SURVEY 8(f)-4 (second half): the float64 Gaussian blur of RSN's legacy decoder
+ * (RSN/exps/RSN18.coco/test.py:39-40: cv2.GaussianBlur on a float64 map, sigma 0).
+ * The arithmetic lives in OpenCV (not vendored; container has 4.13.0).  Probed here against cv2
+ * (tests/test_rsn_legacy.py repeats the probe on whatever host runs it): for CV_64F the row
+ * filter is the generic one -- k[0]*x[0], then a left-to-right chain that the library's build
+ * FUSES (fma) -- and the column filter is the symmetric one -- k[c]*x[c], then
+ * + k[c+i]*(x[c+i] + x[c-i]) with a separately rounded multiply and add.  Border: reflect-101.
+ * `k` is cv2.getGaussianKernel(n, 0, CV_64F) (tables in oracle.py, taken from cv2 itself).
+ * ------------------------------------------------------------------------------------- */
+void udp_o_gaussian_blur_f64(const double *src, double *dst, int h, int w, int n, const double *k)
+{
+    const int r = n / 2;
+    double *t = (double *)malloc(sizeof(double) * (size_t)h * w);
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            double s = k[0] * src[y * w + reflect101(x - r, w)];
+            for (int i = 1; i < n; ++i) s = fma(k[i], src[y * w + reflect101(x - r + i, w)], s);
+            t[y * w + x] = s;
+        }
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            double s = k[r] * t[y * w + x];
+            for (int i = 1; i <= r; ++i) {
+                const double pair = t[reflect101(y + i, h) * w + x] + t[reflect101(y - i, h) * w + x];
+                const double prod = k[r + i] * pair;
+                s = s + prod;
+            }
+            dst[y * w + x] = s;
+        }
+    free(t);
+}
