@@ -171,6 +171,19 @@ int udp_accuracy_pck(const float *output, const float *target, int ch_stride, in
 int udp_decode_quarter(const float *heatmaps, const void *boxes, int boxes_f64, int K, int w, int h, int N,
                        int32_t *coords, float *coords_f32, float *maxvals, void *stream);
 
+/* SURVEY 8(f)-4 (second half)  RSN's legacy decoder: get_results(outputs, centers, scales, kernel, shifts)
+ *     of RSN/exps/RSN18.coco/test.py:25-71 (also Res18.coco, 4XRSN18.coco, RSN18.mpii), with the flip
+ *     average of compute_on_dataset (:88-96) fused when outputs_flipped is given (flip_perm [K] int32).
+ *     outputs [N,K,h,w] float32 (network units, 255 * heat); centers/scales [N,2] float32 (scales NOT yet
+ *     multiplied by 200 -- the reference's in-place `scales *= 200` happens inside); (in_w, in_h) =
+ *     cfg.INPUT_SHAPE[1], [0]; kernel = cfg.TEST.GAUSSIAN_KERNEL (odd, 3..15) and taps_host = HOST pointer
+ *     to its `kernel` float64 taps, cv2.getGaussianKernel(kernel, 0, CV_64F); shift = cfg.TEST.SHIFT_RATIOS[0].
+ *     Out: preds [N,K,2] float64, maxvals [N,K,1] float64.  Maps containing NaN are not supported. */
+int udp_rsn_get_results(const float *outputs, const float *outputs_flipped, const int32_t *flip_perm,
+                        const float *centers, const float *scales, int K, int w, int h, int in_w, int in_h,
+                        int kernel, const double *taps_host, double shift, double *preds, double *maxvals,
+                        int N, void *stream);
+
 /* SURVEY 8(f)-3  COCO rescoring: deep_hrnet/lib/dataset/coco.py:326-339.
  *     preds [N,K,3] float32 (x, y, maxval -- the rows of validate()'s all_preds, function.py:208-209),
  *     box_score [N] float64 (all_boxes[:,5]).  score[n] = mean(maxval > in_vis_thre) * box_score[n]

@@ -39,3 +39,45 @@ def test_oracle_get_results_matches_reference(case):
     N, K, osh, ish, ksz, _ = G.CASES[case]
     out, c, s = G.inputs(case)
     _check(case, *O.rsn_get_results(out, c, s, ish, ksz))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", sorted(G.CASES))
+def test_device_get_results_matches_reference(case):
+    from udp_pose_b200 import reference_api as R
+    N, K, osh, ish, ksz, _ = G.CASES[case]
+    out, c, s = G.inputs(case)
+    s0 = s.copy()
+    _check(case, *R.rsn_legacy_get_results(out, c, s, ksz, [0.25], input_shape=ish))
+    assert np.array_equal(s, s0)
+
+
+@pytest.mark.gpu
+def test_device_get_results_flip_fused_and_large():
+    """1024 persons with the flip test fused, against the oracle run on the host-side average
+    (flip_back of RSN/lib/utils/transforms.py:59-67, then (a + b) * 0.5)."""
+    import torch
+    from udp_pose_b200 import device_api as D, reference_api as R, synth
+    from udp_pose_b200.configs import CONFIGS
+    cfg = CONFIGS[5]
+    rng = np.random.default_rng(8)
+    out, fl = synth.heatmaps(cfg, 1024, rng)
+    c, s, _ = synth.boxes(cfg, 1024, rng)
+    c, s = c.astype(np.float32), s.astype(np.float32)
+    avg = O.flip_average(out, fl, cfg.flip_pairs)
+    want = O.rsn_get_results(avg[:96], c[:96], s[:96], (256, 192), 5)
+    got = R.rsn_legacy_get_results(torch.from_numpy(out).cuda(), c, s, 5, [0.25], outputs_flipped=torch.from_numpy(fl).cuda(),
+                                   flip_pairs=cfg.flip_pairs)
+    assert np.array_equal(got[0][:96], want[0]) and np.array_equal(got[1][:96], want[1])
+    # the fused flip equals decoding the device-side average
+    d_avg = D.flip_back(torch.from_numpy(fl).cuda(), cfg.flip_pairs, False)
+    both = (torch.from_numpy(out).cuda() + d_avg) * 0.5
+    again = R.rsn_legacy_get_results(both, c, s, 5, [0.25])
+    assert np.array_equal(got[0], again[0]) and np.array_equal(got[1], again[1])
+
+
+def test_product_tap_tables_match_cv2():
+    cv2 = pytest.importorskip("cv2")
+    from udp_pose_b200 import device_api as D
+    for n in (5, 7, 9, 11, 13, 15):
+        assert np.array_equal(D.cv_gauss_taps_f64(n), cv2.getGaussianKernel(n, 0, cv2.CV_64F).ravel())

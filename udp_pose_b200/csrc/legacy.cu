@@ -1,0 +1,162 @@
+// legacy.cu -- SURVEY 8(f)-4 (second half): RSN's legacy (biased) decoder.
+//
+// Reference: get_results of RSN/exps/RSN18.coco/test.py:25-71 (the same function in the Res18.coco,
+// 4XRSN18.coco and RSN18.mpii experiments), called from compute_on_dataset (:74-103) after the flip
+// average (:88-96, RSN/lib/utils/transforms.py:59-67).  Per map the reference copies the float32
+// network output into a zero float64 array with a 10-pixel border, runs cv2.GaussianBlur
+// (kernel cfg.TEST.GAUSSIAN_KERNEL: 5 for COCO, 9 for MPII, RSN/dataset/attribute.py:49,92; 11 is
+// the function's default), takes the arg-max, zeroes it, takes the arg-max again, moves a quarter
+// pixel from the first towards the second, clamps, maps `x*4+2` through the biased affine and
+// reads the score (out/255 + 0.5) at the rounded position.
+//
+// One CTA per map.  The (flip-averaged) float32 map is staged in shared memory inside a zero frame,
+// the row pass writes float64 rows, the column pass is evaluated on the fly over the whole padded
+// domain and reduced to the two best (value, first index) candidates -- the blurred map is never
+// stored, and "zero the maximum, search again" becomes a comparison of the runner-up with a zero
+// at the winner's index.  The blur reproduces OpenCV's CV_64F path operation by operation (probed
+// against cv2, tests/test_rsn_legacy.py): row filter = k[0]*x[0] then a FUSED left-to-right chain,
+// column filter = k[c]*x[c] then separately rounded + k[c+i]*(x[c+i] + x[c-i]); taps that fall on
+// the zero frame are multiplied and added like any other, so signed zeros come out the same.
+// FP64-bound (2n fused/unfused multiply-adds per padded element), not HBM-bound.  Maps with NaN are
+// not supported (np.argmax's NaN rule is not reproduced here).
+#include <math.h>
+
+#include "common.cuh"
+
+namespace udp {
+
+constexpr int LG_THREADS = 256;
+constexpr int LG_BORDER = 10;   // test.py:36
+constexpr int LG_MAXK = 15;
+
+struct LegacyArgs {
+    const float *out, *out_flipped;
+    const int32_t *flip_perm;
+    const float *center, *scale;
+    double *preds, *maxvals;
+    double k[LG_MAXK];
+    double shift;
+    int K, w, h, in_w, in_h, n;
+};
+
+// (va, ia) ranks before (vb, ib): larger value, then lower index (np.argmax's first-index rule)
+__device__ __forceinline__ bool lg_before(double va, int ia, double vb, int ib) { return va > vb || (va == vb && ia < ib); }
+
+struct Top2 {
+    double v1, v2;
+    int i1, i2;
+    __device__ __forceinline__ void init() { v1 = v2 = -INFINITY; i1 = i2 = 0x7fffffff; }
+    __device__ __forceinline__ void push(double v, int i)
+    {
+        if (lg_before(v, i, v1, i1)) { v2 = v1; i2 = i1; v1 = v; i1 = i; }
+        else if (lg_before(v, i, v2, i2)) { v2 = v; i2 = i; }
+    }
+};
+
+__global__ void __launch_bounds__(LG_THREADS)
+rsn_get_results_kernel(const __grid_constant__ LegacyArgs p)
+{
+    extern __shared__ __align__(16) unsigned char lg_smem[];
+    __shared__ Top2 s_red[LG_THREADS / 32];
+    const int w = p.w, h = p.h, n = p.n, r = n >> 1, B = LG_BORDER;
+    const int PW = w + 2 * B, PH = h + 2 * B, SW = PW + 2 * r;
+    double *T = reinterpret_cast<double *>(lg_smem);             // [h][PW] row-pass result (inner rows only)
+    float *S = reinterpret_cast<float *>(T + (size_t)h * PW);    // [h][SW] the map inside its zero frame
+    const long long m = blockIdx.x;
+    const int person = (int)(m / p.K), joint = (int)(m - (long long)person * p.K);
+    const float *src = p.out + m * (long long)(h * w);
+    const float *fl = p.out_flipped ? p.out_flipped + ((long long)person * p.K + p.flip_perm[joint]) * (long long)(h * w) : nullptr;
+    for (int i = threadIdx.x; i < h * SW; i += LG_THREADS) {
+        const int y = i / SW, q = i - y * SW, x = q - r - B;
+        float v = 0.0f;
+        if (x >= 0 && x < w) {
+            v = src[y * w + x];
+            if (fl) v = __fmul_rn(__fadd_rn(v, fl[y * w + (w - 1 - x)]), 0.5f);  // flip_back + average (test.py:92-96)
+        }
+        S[i] = v;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < h * PW; i += LG_THREADS) {    // row pass: fused chain, left to right
+        const int y = i / PW, xp = i - y * PW;
+        const float *s = S + y * SW + xp;
+        double acc = __dmul_rn(p.k[0], (double)s[0]);
+        for (int t = 1; t < n; ++t) acc = fma(p.k[t], (double)s[t], acc);
+        T[i] = acc;
+    }
+    __syncthreads();
+    Top2 best;
+    best.init();
+    for (int i = threadIdx.x; i < PH * PW; i += LG_THREADS) {   // column pass over the whole padded domain
+        const int yp = i / PW, xp = i - yp * PW, y = yp - B;
+        auto row = [&](int yy) { return (yy >= 0 && yy < h) ? T[yy * PW + xp] : 0.0; };
+        double acc = __dmul_rn(p.k[r], row(y));
+        for (int t = 1; t <= r; ++t) acc = __dadd_rn(acc, __dmul_rn(p.k[r + t], __dadd_rn(row(y + t), row(y - t))));
+        best.push(acc, i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov1 = __shfl_xor_sync(0xffffffffu, best.v1, o), ov2 = __shfl_xor_sync(0xffffffffu, best.v2, o);
+        const int oi1 = __shfl_xor_sync(0xffffffffu, best.i1, o), oi2 = __shfl_xor_sync(0xffffffffu, best.i2, o);
+        best.push(ov1, oi1);
+        best.push(ov2, oi2);
+    }
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    for (int q = 1; q < LG_THREADS / 32; ++q) {
+        best.push(s_red[q].v1, s_red[q].i1);
+        best.push(s_red[q].v2, s_red[q].i2);
+    }
+    // first arg-max, then arg-max of the map with that element set to 0 (test.py:44-50)
+    const int i1 = best.i1;
+    const int i2 = lg_before(0.0, i1, best.v2, best.i2) ? i1 : best.i2;
+    const int yi = i1 / PW - B, xi = i1 % PW - B;
+    const int px = (i2 % PW) - (i1 % PW), py = (i2 / PW) - (i1 / PW);
+    double x = (double)xi, y = (double)yi;
+    const double ln = __dsqrt_rn((double)(px * px + py * py));  // int ** 0.5: numpy's sqrt fast path
+    if (ln > 1e-3) {
+        x = __dadd_rn(x, __ddiv_rn(__dmul_rn(p.shift, (double)px), ln));
+        y = __dadd_rn(y, __ddiv_rn(__dmul_rn(p.shift, (double)py), ln));
+    }
+    x = fmax(0.0, fmin(x, (double)(w - 1)));
+    y = fmax(0.0, fmin(y, (double)(h - 1)));
+    const int rx = (int)rint(x), ry = (int)rint(y);               // round(): half to even
+    const float raw = S[ry * SW + rx + r + B];
+    const float score = __fadd_rn(__fdiv_rn(raw, 255.0f), 0.5f);   // score_map = out / 255 + 0.5 (float32)
+    const float s0 = __fmul_rn(p.scale[2 * person], 200.0f), s1 = __fmul_rn(p.scale[2 * person + 1], 200.0f);  // scales *= 200 (float32)
+    const double kx = __dadd_rn(__dmul_rn(x, 4.0), 2.0), ky = __dadd_rn(__dmul_rn(y, 4.0), 2.0);
+    p.preds[2 * m] = __dsub_rn(__dadd_rn(__dmul_rn(__ddiv_rn(kx, (double)p.in_w), (double)s0), (double)p.center[2 * person]),
+                               (double)__fmul_rn(s0, 0.5f));
+    p.preds[2 * m + 1] = __dsub_rn(__dadd_rn(__dmul_rn(__ddiv_rn(ky, (double)p.in_h), (double)s1), (double)p.center[2 * person + 1]),
+                                   (double)__fmul_rn(s1, 0.5f));
+    p.maxvals[m] = (double)score;
+}
+
+}  // namespace udp
+
+extern "C" int udp_rsn_get_results(const float *outputs, const float *outputs_flipped, const int32_t *flip_perm,
+                                   const float *centers, const float *scales, int K, int w, int h, int in_w, int in_h,
+                                   int kernel, const double *taps_host, double shift, double *preds, double *maxvals,
+                                   int N, void *stream)
+{
+    if (N < 0 || K < 1 || w < 1 || h < 1 || in_w < 1 || in_h < 1) return UDP_EINVAL;
+    if (kernel < 3 || kernel > udp::LG_MAXK || !(kernel & 1) || !taps_host) return UDP_EINVAL;
+    if (N == 0) return 0;
+    if (!outputs || !centers || !scales || !preds || !maxvals || (outputs_flipped && !flip_perm)) return UDP_EINVAL;
+    const long long maps = (long long)N * K;
+    if (maps > 0x7fffffffLL) return UDP_EINVAL;
+    udp::LegacyArgs a;
+    a.out = outputs; a.out_flipped = outputs_flipped; a.flip_perm = flip_perm;
+    a.center = centers; a.scale = scales; a.preds = preds; a.maxvals = maxvals;
+    for (int i = 0; i < udp::LG_MAXK; ++i) a.k[i] = i < kernel ? taps_host[i] : 0.0;
+    a.shift = shift;
+    a.K = K; a.w = w; a.h = h; a.in_w = in_w; a.in_h = in_h; a.n = kernel;
+    const int PW = w + 2 * udp::LG_BORDER, SW = PW + 2 * (kernel >> 1);
+    const size_t smem = (size_t)h * PW * sizeof(double) + (size_t)h * SW * sizeof(float);
+    if (smem > 200 * 1024) return UDP_EINVAL;
+    cudaError_t e = cudaFuncSetAttribute(udp::rsn_get_results_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    udp::rsn_get_results_kernel<<<(unsigned)maps, udp::LG_THREADS, smem, (cudaStream_t)stream>>>(a);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}

@@ -437,3 +437,47 @@ def decode_quarter(heatmaps, boxes, want_float=False):
     _lib.call("udp_decode_quarter", _ptr(heatmaps), _ptr(boxes), int(boxes.dtype == _F64), int(K), int(w), int(h), int(N),
               _ptr(out), _ptr(cf), _ptr(mv), _stream())
     return (out, cf, mv) if want_float else out
+
+
+# cv2.getGaussianKernel(n, 0, cv2.CV_64F)[: n // 2 + 1] (OpenCV 4.x: fixed tables up to 9, bit-exact exp beyond;
+# tests/test_rsn_legacy.py checks them against the installed cv2)
+_CV_GAUSS_F64 = {
+    5: ['0x1.0000000000000p-4', '0x1.0000000000000p-2', '0x1.8000000000000p-2'],
+    7: ['0x1.0000000000000p-5', '0x1.c000000000000p-4', '0x1.c000000000000p-3', '0x1.2000000000000p-2'],
+    9: ['0x1.0000000000000p-6', '0x1.a000000000000p-5', '0x1.e000000000000p-4', '0x1.9800000000000p-3', '0x1.e000000000000p-3'],
+    11: ['0x1.20c2564ee6772p-7', '0x1.bcb86a082c301p-6', '0x1.0ab50979aaf94p-4', '0x1.f2464c62edaf4p-4', '0x1.6a7e1d504a91dp-3',
+         '0x1.9ac20a36ea596p-3'],
+    13: ['0x1.7c090614dc85bp-8', '0x1.0cb82167c249dp-6', '0x1.3a8fe850a8f47p-5', '0x1.30cd237f01688p-4', '0x1.e8f1e9d4d4f8bp-4',
+         '0x1.449ed5bf3520ap-3', '0x1.64ccba4a2c88fp-3'],
+    15: ['0x1.0d2c46a814066p-8', '0x1.600a4b3638a7bp-7', '0x1.8d1b96696e28fp-6', '0x1.825954ed343f3p-5', '0x1.4431ed85d4175p-4',
+         '0x1.d543dae40f820p-4', '0x1.24ec9c4a6087bp-3', '0x1.3b69611f1d587p-3'],
+}
+
+
+def cv_gauss_taps_f64(n):
+    if n not in _CV_GAUSS_F64:
+        raise ValueError("GAUSSIAN_KERNEL %r: supported sizes are %s" % (n, sorted(_CV_GAUSS_F64)))
+    half = [float.fromhex(v) for v in _CV_GAUSS_F64[n]]
+    return np.array(half + half[-2::-1], np.float64)
+
+
+def rsn_get_results(outputs, centers, scales, input_shape, kernel=11, shift=0.25, outputs_flipped=None, flip_pairs=None):
+    """SURVEY 8(f)-4 (second half): get_results of RSN/exps/RSN18.coco/test.py:25-71 for a batch, the flip
+    average of :88-96 fused when outputs_flipped is given.  outputs f32 CUDA [N,K,h,w]; centers/scales f32
+    [N,2] (scales as the loader yields them, not yet x200); input_shape = (H, W) = cfg.INPUT_SHAPE.
+    Returns (preds f64 [N,K,2], maxvals f64 [N,K,1]) CUDA tensors."""
+    outputs = _dev(outputs, _F32)
+    centers, scales = _dev(centers, _F32), _dev(scales, _F32)
+    N, K, h, w = outputs.shape
+    fl = perm = None
+    if outputs_flipped is not None:
+        fl = _dev(outputs_flipped, _F32)
+        assert fl.shape == outputs.shape
+        perm = flip_perm(K, flip_pairs or [], outputs.device)
+    taps = cv_gauss_taps_f64(int(kernel))
+    preds = torch.empty((N, K, 2), dtype=_F64, device=outputs.device)
+    maxvals = torch.empty((N, K, 1), dtype=_F64, device=outputs.device)
+    _lib.call("udp_rsn_get_results", _ptr(outputs), _ptr(fl), _ptr(perm), _ptr(centers), _ptr(scales), int(K), int(w), int(h),
+              int(input_shape[1]), int(input_shape[0]), int(kernel), taps.ctypes.data_as(C.c_void_p), float(shift),
+              _ptr(preds), _ptr(maxvals), int(N), _stream())
+    return preds, maxvals

@@ -401,6 +401,30 @@ def demo_get_final_preds(heatmaps, boxes):
     return out
 
 
+def rsn_legacy_get_results(outputs, centers, scales, kernel=11, shifts=(0.25,), input_shape=None,
+                           outputs_flipped=None, flip_pairs=None):
+    """RSN/exps/RSN18.coco/test.py:25-71 `get_results(outputs, centers, scales, kernel, shifts)` (the
+    non-prm RSN experiments).  The reference reads cfg.INPUT_SHAPE / OUTPUT_SHAPE / KEYPOINT.NUM from its
+    experiment config: here the output shape and joint count come from `outputs`, and input_shape
+    defaults to 4x the output shape (RSN/dataset/attribute.py:19-20, 62-63).  Only one shift ratio is
+    supported (cfg.TEST.SHIFT_RATIOS = [0.25] in every experiment).  Unlike the reference (:26) the
+    caller's `scales` array is not multiplied by 200 in place.  With outputs_flipped (already run through
+    the model, NOT yet flipped back) the flip average of compute_on_dataset (:88-96) is fused.
+    Returns (preds float64 [N,K,2], maxvals float64 [N,K,1])."""
+    if len(shifts) != 1:
+        raise NotImplementedError("get_results: one shift ratio (cfg.TEST.SHIFT_RATIOS = [0.25])")
+    o = outputs if isinstance(outputs, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(outputs, np.float32))
+    f = outputs_flipped
+    if f is not None and not isinstance(f, torch.Tensor):
+        f = torch.from_numpy(np.ascontiguousarray(f, np.float32))
+    h, w = o.shape[2], o.shape[3]
+    ish = tuple(input_shape) if input_shape is not None else (4 * h, 4 * w)
+    c = np.ascontiguousarray(_np(centers) if isinstance(centers, torch.Tensor) else centers, np.float32)
+    s = np.ascontiguousarray(_np(scales) if isinstance(scales, torch.Tensor) else scales, np.float32)
+    preds, maxvals = D.rsn_get_results(o, c, s, ish, kernel, shifts[0], f, flip_pairs)
+    return _np(preds), _np(maxvals)
+
+
 def _nms_one(kpts_db, thresh, sigmas, in_vis_thre, soft):
     if len(kpts_db) == 0:
         return []
