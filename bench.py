@@ -544,6 +544,27 @@ def run_ours(args):
         fused["decode_quarter"] = {"ms": round(a.elapsed_time(b) / reps, 4), "bytes_per_person": cfg.channels * h * w * 4.0 + 16 + 8 * cfg.channels,
                                    "maps_per_person": cfg.channels}
 
+    if fused is not None:  # SURVEY 8(f)-4 (second half): RSN's legacy get_results over the same network output
+        qc, qs = wl["center"].float().contiguous(), wl["scale"].float().contiguous()
+        ksz = 9 if cfg.num_joints == 16 else 5   # cfg.TEST.GAUSSIAN_KERNEL: RSN/dataset/attribute.py:49 (COCO), :92 (MPII)
+        nb_l = min(B, 4096)
+        for _ in range(2):
+            D.rsn_get_results(wl["out"][:nb_l], qc[:nb_l], qs[:nb_l], (H, W), ksz)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(5):
+            D.rsn_get_results(wl["out"][:nb_l], qc[:nb_l], qs[:nb_l], (H, W), ksz)
+        b.record()
+        torch.cuda.synchronize()
+        lg_ms = a.elapsed_time(b) / 5
+        legacy = {"ms": round(lg_ms, 4), "persons": nb_l, "maps_per_person": cfg.channels, "gaussian_kernel": ksz,
+                  "persons_per_s": round(nb_l / (lg_ms * 1e-3)),
+                  "achieved_gbs": round((cfg.channels * h * w * 4.0 + 16 + 24 * cfg.channels) * nb_l / (lg_ms * 1e-3) / 1e9, 1),
+                  "note": "udp_rsn_get_results (RSN/exps/RSN18.coco/test.py:25-71): float64 blur of the zero-padded map + top-2 arg-max, "
+                          "issue-bound (77 % issue-active, DRAM 3 %), no HBM roofline claimed"}
+    else:
+        legacy = None
+
     # ---- SURVEY 8(f)-3 (outside the timed step): COCO rescoring + OKS-NMS of B pose results, one CTA per image
     nms = None
     if world == 1 and not args.no_fused:
@@ -692,12 +713,14 @@ def run_ours(args):
         for v in fused.values():
             v["achieved_gbs"] = round(v["bytes_per_person"] * B / (v["ms"] * 1e-3) / 1e9, 1)
             v["frac"] = round(v["achieved_gbs"] / peak, 4)
-        line["next"] = dict(fused, note="SURVEY 8(f) ranks 1-3, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
+        line["next"] = dict(fused, note="SURVEY 8(f) ranks 1-4, timed outside the step: udp_warp_affine_normalize_f32 writes Normalize(ToTensor(crop)) "
                                         "as float32 CHW (and the x-mirrored flip-test input) straight from the gather; udp_accuracy_pck is evaluate.py:accuracy "
                                         "on device tensors; udp_decode_quarter is tools/infer_utils/decode.py:get_final_preds over every channel of the same output; "
                                         "oks_nms is coco.py:321-356; none is part of `value`")
     if nms:
         line.setdefault("next", {})["oks_nms"] = nms
+    if legacy:
+        line.setdefault("next", {})["rsn_get_results"] = legacy
     if e2e:
         line["e2e"] = e2e
     if not args.no_cpu and world == 1:

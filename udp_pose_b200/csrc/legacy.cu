@@ -53,45 +53,67 @@ struct Top2 {
     }
 };
 
+// NK = the kernel size when known at compile time (5: COCO, 9: MPII, 11: the function's default), 0 = p.n
+template <int NK>
 __global__ void __launch_bounds__(LG_THREADS)
 rsn_get_results_kernel(const __grid_constant__ LegacyArgs p)
 {
     extern __shared__ __align__(16) unsigned char lg_smem[];
     __shared__ Top2 s_red[LG_THREADS / 32];
-    const int w = p.w, h = p.h, n = p.n, r = n >> 1, B = LG_BORDER;
+    const int w = p.w, h = p.h, n = NK ? NK : p.n, r = n >> 1, B = LG_BORDER;
     const int PW = w + 2 * B, PH = h + 2 * B, SW = PW + 2 * r;
-    double *T = reinterpret_cast<double *>(lg_smem);             // [h][PW] row-pass result (inner rows only)
-    float *S = reinterpret_cast<float *>(T + (size_t)h * PW);    // [h][SW] the map inside its zero frame
+    double *T0 = reinterpret_cast<double *>(lg_smem);            // [2r + h + 2r][PW] row-pass result inside 2r zero rows
+    double *T = T0 + 2 * r * PW;                                 // row 0 of the map
+    float *S = reinterpret_cast<float *>(T0 + (size_t)(h + 4 * r) * PW);  // [h][SW] the map inside its zero frame
     const long long m = blockIdx.x;
     const int person = (int)(m / p.K), joint = (int)(m - (long long)person * p.K);
     const float *src = p.out + m * (long long)(h * w);
     const float *fl = p.out_flipped ? p.out_flipped + ((long long)person * p.K + p.flip_perm[joint]) * (long long)(h * w) : nullptr;
-    for (int i = threadIdx.x; i < h * SW; i += LG_THREADS) {
-        const int y = i / SW, q = i - y * SW, x = q - r - B;
-        float v = 0.0f;
-        if (x >= 0 && x < w) {
-            v = src[y * w + x];
-            if (fl) v = __fmul_rn(__fadd_rn(v, fl[y * w + (w - 1 - x)]), 0.5f);  // flip_back + average (test.py:92-96)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int NWARP = LG_THREADS / 32;
+    for (int i = threadIdx.x; i < 2 * r * PW; i += LG_THREADS) { T0[i] = 0.0; T[h * PW + i] = 0.0; }
+    // warp per row, lanes along the row: no divisions, and the row tests below are warp-uniform
+    for (int y = warp; y < h; y += NWARP) {
+        float *srow = S + y * SW;
+        for (int q = lane; q < SW; q += 32) {
+            const int x = q - r - B;
+            float v = 0.0f;
+            if (x >= 0 && x < w) {
+                v = src[y * w + x];
+                if (fl) v = __fmul_rn(__fadd_rn(v, fl[y * w + (w - 1 - x)]), 0.5f);  // flip_back + average (test.py:92-96)
+            }
+            srow[q] = v;
         }
-        S[i] = v;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < h * PW; i += LG_THREADS) {    // row pass: fused chain, left to right
-        const int y = i / PW, xp = i - y * PW;
-        const float *s = S + y * SW + xp;
-        double acc = __dmul_rn(p.k[0], (double)s[0]);
-        for (int t = 1; t < n; ++t) acc = fma(p.k[t], (double)s[t], acc);
-        T[i] = acc;
+    for (int y = warp; y < h; y += NWARP) {                      // row pass: fused chain, left to right
+        const float *srow = S + y * SW;
+        for (int xp = lane; xp < PW; xp += 32) {
+            double acc = __dmul_rn(p.k[0], (double)srow[xp]);
+#pragma unroll
+            for (int t = 1; t < n; ++t) acc = fma(p.k[t], (double)srow[xp + t], acc);
+            T[y * PW + xp] = acc;
+        }
     }
     __syncthreads();
     Top2 best;
     best.init();
-    for (int i = threadIdx.x; i < PH * PW; i += LG_THREADS) {   // column pass over the whole padded domain
-        const int yp = i / PW, xp = i - yp * PW, y = yp - B;
-        auto row = [&](int yy) { return (yy >= 0 && yy < h) ? T[yy * PW + xp] : 0.0; };
-        double acc = __dmul_rn(p.k[r], row(y));
-        for (int t = 1; t <= r; ++t) acc = __dadd_rn(acc, __dmul_rn(p.k[r + t], __dadd_rn(row(y + t), row(y - t))));
-        best.push(acc, i);
+    for (int yp = warp; yp < PH; yp += NWARP) {                  // column pass over the whole padded domain
+        const int y = yp - B;
+        if (y + r < 0 || y - r >= h) {
+            // every tap lies in the zero frame: k*0 + k*(0 + 0) ... = +0 exactly, nothing to load
+            // (a thread walks its elements in index order, so only a strictly larger value can enter its pair)
+            for (int xp = lane; xp < PW; xp += 32)
+                if (0.0 > best.v2) best.push(0.0, yp * PW + xp);
+            continue;
+        }
+        for (int xp = lane; xp < PW; xp += 32) {
+            const double *c = T + y * PW + xp;   // rows y - r .. y + r exist: the map sits inside 2r zero rows
+            double acc = __dmul_rn(p.k[r], c[0]);
+#pragma unroll
+            for (int t = 1; t <= r; ++t) acc = __dadd_rn(acc, __dmul_rn(p.k[r + t], __dadd_rn(c[t * PW], c[-t * PW])));
+            if (acc > best.v2) best.push(acc, yp * PW + xp);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -152,11 +174,14 @@ extern "C" int udp_rsn_get_results(const float *outputs, const float *outputs_fl
     a.shift = shift;
     a.K = K; a.w = w; a.h = h; a.in_w = in_w; a.in_h = in_h; a.n = kernel;
     const int PW = w + 2 * udp::LG_BORDER, SW = PW + 2 * (kernel >> 1);
-    const size_t smem = (size_t)h * PW * sizeof(double) + (size_t)h * SW * sizeof(float);
+    const size_t smem = (size_t)(h + 4 * (kernel >> 1)) * PW * sizeof(double) + (size_t)h * SW * sizeof(float);
     if (smem > 200 * 1024) return UDP_EINVAL;
-    cudaError_t e = cudaFuncSetAttribute(udp::rsn_get_results_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    void (*kern)(udp::LegacyArgs) = kernel == 5 ? udp::rsn_get_results_kernel<5>
+                                  : kernel == 9 ? udp::rsn_get_results_kernel<9>
+                                  : kernel == 11 ? udp::rsn_get_results_kernel<11> : udp::rsn_get_results_kernel<0>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    udp::rsn_get_results_kernel<<<(unsigned)maps, udp::LG_THREADS, smem, (cudaStream_t)stream>>>(a);
+    kern<<<(unsigned)maps, udp::LG_THREADS, smem, (cudaStream_t)stream>>>(a);
     UDP_LAUNCH_CHECK();
     return 0;
 }
