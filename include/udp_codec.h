@@ -184,6 +184,20 @@ int udp_rsn_get_results(const float *outputs, const float *outputs_flipped, cons
                         int kernel, const double *taps_host, double shift, double *preds, double *maxvals,
                         int N, void *stream);
 
+/* SURVEY 8(f)-5  AID augmentations on the crop: Cutout (deep_hrnet/lib/utils/transforms.py:186-223) and
+ *     HideAndSeek (:144-183), applied in place to the uint8 crops [N,H,W,3] (JointsDataset.py:230-235).
+ *     The random draws stay on the host (numpy's global generator, in the reference's order); this entry
+ *     point applies the drawn parameters:
+ *     ellipses [N,max_ellipses,4] float64 (cx, cy, rx, ry; :205-206), n_ellipses [N] int32 (0 = Cutout not
+ *     applied to this person), max_ellipses <= 8; either may be NULL (no Cutout).
+ *     grid_size [N] int32 (0 = HideAndSeek not applied / grid 0) and hide_mask [N,8] uint32: bit c of the
+ *     256-bit mask = cell c hidden, cells numbered in the reference's draw order (outer range(0, width, g),
+ *     inner range(0, height, g)); either may be NULL.  min_grid = smallest non-zero grid size in use
+ *     (cells must fit the mask).  The reference's transposed slice img[x:x_end, y:y_end] (:175) is kept. */
+int udp_aid_erase(uint8_t *img, int N, int H, int W, const double *ellipses, const int32_t *n_ellipses,
+                  int max_ellipses, const int32_t *grid_size, const uint32_t *hide_mask, int min_grid,
+                  void *stream);
+
 /* SURVEY 8(f)-3  COCO rescoring: deep_hrnet/lib/dataset/coco.py:326-339.
  *     preds [N,K,3] float32 (x, y, maxval -- the rows of validate()'s all_preds, function.py:208-209),
  *     box_score [N] float64 (all_boxes[:,5]).  score[n] = mean(maxval > in_vis_thre) * box_score[n]

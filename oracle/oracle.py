@@ -195,6 +195,26 @@ def rsn_get_results(outputs, centers, scales, in_shape, kernel=11, shift=0.25, b
     return preds, maxvals
 
 
+def aid_erase(img, ellipses=(), grid=0, hidden=()):
+    """Cutout._cutout (deep_hrnet/lib/utils/transforms.py:199-216) and
+    HideAndSeek._hide_and_seek (:163-177) for DRAWN parameters (the random draws are the caller's):
+    ellipses = [(cx, cy, rx, ry), ...]; grid and `hidden` = one flag per cell in draw order (outer loop
+    over range(0, width, grid), inner over range(0, height, grid)); the reference's transposed slice
+    img[x:x_end, y:y_end] is kept.  img uint8 [H,W,3]; returns a new array."""
+    out = np.array(img, copy=True)
+    H, W, _ = out.shape
+    xs, ys = np.meshgrid(np.arange(W), np.arange(H))
+    for cx, cy, rx, ry in ellipses:
+        out[((cx - xs) / rx) ** 2 + ((cy - ys) / ry) ** 2 <= 1] = 0
+    if grid:
+        flags = iter(hidden)
+        for x in range(0, W, grid):
+            for y in range(0, H, grid):
+                if next(flags):
+                    out[x:min(W, x + grid), y:min(H, y + grid), :] = 0
+    return out
+
+
 COCO_SIGMAS = np.array([.26, .25, .25, .35, .35, .79, .79, .72, .72, .62, .62, 1.07, 1.07, .87, .87, .89, .89]) / 10.0
 
 

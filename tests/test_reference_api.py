@@ -143,6 +143,36 @@ def test_getitem_eval_and_train_rng_order(R):
     assert np.array_equal(meta["scale"], s) and meta["rotation"] == r
 
 
+def test_getitem_train_with_aid(R):
+    """JointsDataset.py:96-106, 230-235: with DATASET.CUTOUT / HIDE_AND_SEEK set, the train path erases
+    the crop with parameters drawn after the warp draws, Cutout before HideAndSeek, and leaves numpy's
+    generator where the reference would."""
+    import random
+    from oracle import oracle as O
+    cfg, g = CONFIGS[1], parity.load(1)
+    ycfg = cfg.as_cfg()
+    ycfg.DATASET.CUTOUT, ycfg.DATASET.HIDE_AND_SEEK = [1.0, 0.3, 2], [1.0, 0.5, (16, 32, 0)]
+    ds = R.JointsDataset(ycfg, "", "train", True)
+    plain = R.JointsDataset(cfg.as_cfg(), "", "train", True)
+    for d in (ds, plain):
+        d.num_joints, d.flip_pairs = cfg.num_joints, cfg.flip_pairs
+        d.db = [dict(image="mem://0", joints_3d=g["joints_src"][0].copy(), joints_3d_vis=g["joints_vis"][0].copy(),
+                     center=g["center"][0].copy(), scale=g["scale"][0].copy(), score=1)]
+    img = g["src_images"][g["src_index"][0]]
+    np.random.seed(5); random.seed(5)
+    x_aid, _, _, _ = ds.__getitem__(0, image=img)
+    after = np.random.rand()
+    np.random.seed(5); random.seed(5)
+    x_plain, _, _, _ = plain.__getitem__(0, image=img)
+    ell = R.Cutout(1.0, 0.3, 2).draw(256, 192)
+    grid, bits = R.HideAndSeek(1.0, 0.5, (16, 32, 0)).draw(256, 192)
+    want = O.aid_erase(O.aid_erase(x_plain, ellipses=ell), grid=grid, hidden=bits)
+    assert np.array_equal(x_aid, want) and not np.array_equal(x_aid, x_plain)
+    assert np.random.rand() == after
+    with pytest.raises(NotImplementedError):
+        ds.get_batch([0], [img], normalize=((0.485, 0.456, 0.406), (0.229, 0.224, 0.225)))
+
+
 def test_get_batch_with_fused_normalize(R):
     """get_batch(normalize=(mean, std)) returns what the reference's DataLoader hands the model:
     Normalize(ToTensor(crop)) float32 CHW (tools/train.py:127-143), plus np.flip(input, 3)

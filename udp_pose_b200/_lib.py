@@ -21,6 +21,7 @@ SIGNATURES = {
     "udp_accuracy_pck": [_vp, _vp, _i, _i, _i, _i, _i, C.c_double, _vp, _vp, _vp, _vp, _vp, _vp],
     "udp_decode_quarter": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "udp_rsn_get_results": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _d, _vp, _vp, _i, _vp],
+    "udp_aid_erase": [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _i, _vp],
     "udp_coco_rescore": [_vp, _vp, _i, _i, _d, _vp, _vp],
     "udp_oks_nms": [_vp, _vp, _vp, _vp, _i, _i, _i, _d, _vp, _i, _d, _i, _i, _vp, _vp, _vp, _vp],
     "udp_warp_affine_normalize_f32": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],

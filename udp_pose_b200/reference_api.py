@@ -93,6 +93,91 @@ def flip_joints(joints, joints_vis, width, pairs):
 
 
 # ----------------------------------------------------------------------------- encode side
+class Cutout:
+    """lib/utils/transforms.py:186-223, same constructor.  `draw(height, width)` consumes numpy's global
+    generator exactly as the reference's __call__ does (one rand() for the gate, then per patch two for
+    the centre and rand(2) for the radii) and returns the drawn ellipses [(cx, cy, rx, ry), ...] (empty
+    when the gate fails); the erase itself runs on the device (udp_aid_erase)."""
+
+    def __init__(self, prob=1.0, radius_factor=0.2, num_patch=1):
+        self.prob, self.radius_factor, self.num_patch = prob, radius_factor, num_patch
+        if num_patch > 8:
+            raise ValueError("Cutout: at most 8 patches")
+
+    def draw(self, height, width):
+        out = []
+        if np.random.rand() < self.prob:
+            for _ in range(self.num_patch):
+                center = [np.random.rand() * width, np.random.rand() * height]
+                radius = self.radius_factor * (1 + np.random.rand(2)) * width
+                out.append((center[0], center[1], radius[0], radius[1]))
+        return out
+
+    def __call__(self, img):
+        return _aid_apply(img, [self.draw(img.shape[0], img.shape[1])], None)
+
+
+class HideAndSeek:
+    """lib/utils/transforms.py:144-183, same constructor.  `draw(height, width)` consumes numpy's global
+    generator as the reference does (gate, randint for the grid -- which never picks the last size, :163 --
+    then one rand() per cell, outer loop over the width) and returns (grid_size, [hidden?, ...])."""
+
+    def __init__(self, prob=1.0, prob_hiding_patches=0.5, grid_sizes=(0, 16, 32, 44, 56)):
+        self.prob, self.prob_hiding_patches, self.grid_sizes = prob, prob_hiding_patches, grid_sizes
+
+    def draw(self, height, width):
+        if not np.random.rand() < self.prob:
+            return 0, []
+        g = self.grid_sizes[np.random.randint(0, len(self.grid_sizes) - 1)]
+        bits = []
+        if g != 0:
+            for _x in range(0, width, g):
+                for _y in range(0, height, g):
+                    bits.append(bool(np.random.rand() <= self.prob_hiding_patches))
+        return g, bits
+
+    def __call__(self, img):
+        return _aid_apply(img, None, [self.draw(img.shape[0], img.shape[1])])
+
+
+def _aid_pack(cut, hide, n):
+    """Drawn parameters of n persons -> the arrays udp_aid_erase takes."""
+    ell = ne = gs = mask = None
+    min_grid = 0
+    if cut is not None:
+        P = max(1, max(len(c) for c in cut))
+        ell, ne = np.ones((n, P, 4)), np.zeros(n, np.int32)
+        for i, c in enumerate(cut):
+            ne[i] = len(c)
+            if c:
+                ell[i, :len(c)] = np.asarray(c, np.float64)
+    if hide is not None:
+        gs, mask = np.zeros(n, np.int32), np.zeros((n, 8), np.uint32)
+        for i, (g, bits) in enumerate(hide):
+            if g and any(bits):
+                if len(bits) > 256:
+                    raise ValueError("HideAndSeek: more than 256 cells (grid %d)" % g)
+                gs[i] = g
+                for c, b in enumerate(bits):
+                    if b:
+                        mask[i, c >> 5] |= np.uint32(1 << (c & 31))
+        used = gs[gs > 0]
+        if len(used):
+            min_grid, mask = int(used.min()), mask.view(np.int32)
+        else:
+            gs = mask = None      # nobody drew a grid: nothing to hide
+    return ell, ne, gs, mask, min_grid
+
+
+def _aid_apply(img, cut, hide):
+    """One uint8 HWC image (numpy) through the device erase; returns a new array (the reference
+    writes into its argument and returns it)."""
+    t = torch.from_numpy(np.ascontiguousarray(img)[None]).cuda()
+    ell, ne, gs, mask, mg = _aid_pack(cut, hide, 1)
+    D.aid_erase(t, ell, ne, gs, mask, mg)
+    return _np(t)[0]
+
+
 def half_body_transform(ds, joints, joints_vis):
     """JointsDataset.half_body_transform (:124-167): host-side box selection from the visible
     upper- or lower-body joints; uses np.random exactly once, like the reference."""
@@ -137,9 +222,10 @@ class JointsDataset(torch.utils.data.Dataset):
         self.num_joints_half_body = ds.NUM_JOINTS_HALF_BODY
         self.prob_half_body = ds.PROB_HALF_BODY
         self.color_rgb = ds.COLOR_RGB
-        if getattr(ds, "CUTOUT", None) or getattr(ds, "HIDE_AND_SEEK", None):
-            raise NotImplementedError("AID augmentations (Cutout / HideAndSeek) are outside the codec "
-                                      "path (SURVEY.md 8f rank 5); pass them as `transform`")
+        # AID (JointsDataset.py:96-106): three config values = constructor arguments, anything else truthy = defaults
+        cc, ch = getattr(ds, "CUTOUT", None), getattr(ds, "HIDE_AND_SEEK", None)
+        self.cutout = (Cutout(*cc) if len(cc) == 3 else Cutout()) if cc else None
+        self.hide_and_seek = (HideAndSeek(*ch) if len(ch) == 3 else HideAndSeek()) if ch else None
         self.target_type = cfg.MODEL.TARGET_TYPE
         self.image_size = np.array(cfg.MODEL.IMAGE_SIZE)
         self.heatmap_size = np.array(cfg.MODEL.HEATMAP_SIZE)
@@ -219,10 +305,17 @@ class JointsDataset(torch.utils.data.Dataset):
         test feeds the model (core/function.py:154-155)."""
         W, H = int(self.image_size[0]), int(self.image_size[1])
         recs, imgs, js, vs, cs, ss, rs = [], [], [], [], [], [], []
+        aid = self.is_train and (self.cutout or self.hide_and_seek)
+        if aid and normalize is not None:
+            raise NotImplementedError("AID erases the uint8 crop (JointsDataset.py:230-235): use the uint8 path, then normalise")
+        cuts, hides = [], []
         for n, idx in enumerate(indices):
             rec = copy.deepcopy(self.db[idx])
             img = images[n] if images is not None else self._read(rec["image"])
             img, j, v, c, s, r = self._augment(rec, img)
+            if aid:  # drawn per record, after the warp parameters and in the reference's order (:231-235)
+                cuts.append(self.cutout.draw(H, W) if self.cutout else [])
+                hides.append(self.hide_and_seek.draw(H, W) if self.hide_and_seek else (0, []))
             recs.append(rec); imgs.append(torch.from_numpy(np.ascontiguousarray(img)))
             js.append(j); vs.append(v); cs.append(c); ss.append(s); rs.append(float(r))
         c, s = _csN(np.stack(cs), np.stack(ss))
@@ -233,6 +326,9 @@ class JointsDataset(torch.utils.data.Dataset):
             inp = D.crop_normalize_batch(src, M, (W, H), normalize[0], normalize[1], want_flipped=want_flipped)
         else:
             inp = D.crop_batch(src, M, (W, H))
+            if aid:
+                ell, ne, gs, mask, mg = _aid_pack(cuts if self.cutout else None, hides if self.hide_and_seek else None, len(recs))
+                D.aid_erase(inp, ell, ne, gs, mask, mg)
         j = np.ascontiguousarray(np.stack(js), np.float64)
         jd = torch.from_numpy(j).cuda()
         D.rotate_points_batch(jd, rot, c, s, (W, H), do_clip=False, out=jd)
