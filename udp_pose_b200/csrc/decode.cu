@@ -509,7 +509,10 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
             UDP_LAUNCH_CHECK();                                                                  \
             return 0;                                                                            \
         } while (0);
-        UDP_GAUSS_PIPE(48, 64, 96, 4)
+#ifndef UDP_GAUSS_MINB
+#define UDP_GAUSS_MINB 4
+#endif
+        UDP_GAUSS_PIPE(48, 64, 96, UDP_GAUSS_MINB)
         UDP_GAUSS_PIPE(64, 64, 128, 3)
         UDP_GAUSS_PIPE(72, 96, 288, 2)
 #undef UDP_GAUSS_PIPE

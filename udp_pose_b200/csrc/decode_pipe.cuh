@@ -85,7 +85,9 @@ struct PipeGeom {
     static constexpr int RS = H / YS;
     static constexpr int SR = (W / 4) % 2 == 1 ? W : W + 4;  // raw row stride, SR/4 odd
     static constexpr int ST = W + 2;                      // T row stride
-    static constexpr int TROWS = H + 2 * R;
+    static constexpr int TROWS = H;                       // no halo rows: the column pass reflects its row index (4 % faster than
+                                                          // writing R reflected rows above and below, and T fits the raw buffer)
+    static constexpr int TOFF = 0;
     static constexpr int RAW = H * SR;                    // floats per raw tensor
     static constexpr int BUF0 = (RAW > TROWS * ST) ? RAW : TROWS * ST;
     static constexpr int BUF = ((BUF0 + 31) / 32) * 32;   // one buffer, a multiple of 128 bytes (TMA destination)
@@ -203,7 +205,7 @@ __device__ __forceinline__ void pipe_window(const float *raw_out, const float *r
     }
 }
 
-// Row filter from the register window into T (stride ST, R halo rows above and below).
+// Row filter from the register window into T (stride ST, H rows).
 template <int W, int H, int R, int NT>
 __device__ __forceinline__ void pipe_row_filter(const f32x2 (&v)[PipeGeom<W, H, R, NT>::NCOL],
                                                 float *T, int p, int xs)
@@ -211,11 +213,7 @@ __device__ __forceinline__ void pipe_row_filter(const f32x2 (&v)[PipeGeom<W, H, 
     using G = PipeGeom<W, H, R, NT>;
     constexpr int PAD = G::PAD, SEG = G::SEG;
     const int x0 = xs * SEG, y0 = p, y1 = p + G::HP;
-    float *t0 = T + (y0 + R) * G::ST + x0, *t1 = T + (y1 + R) * G::ST + x0;
-    // reflected halo rows: T row -r = row r (1..R) is owned by y0 = r; row H-1+r = row H-1-r by y1
-    const bool top = (y0 >= 1 && y0 <= R), bot = (y1 >= H - 1 - R && y1 <= H - 2);
-    float *h0 = T + (R - y0) * G::ST + x0;
-    float *h1 = T + (2 * (H - 1) - y1 + R) * G::ST + x0;
+    float *t0 = T + (y0 + G::TOFF) * G::ST + x0, *t1 = T + (y1 + G::TOFF) * G::ST + x0;
 #pragma unroll
     for (int o = 0; o < SEG; o += 2) {
         f32x2 s0 = fmul2p(v[PAD - R + o], Taps<R>::k(0)), s1 = fmul2p(v[PAD - R + o + 1], Taps<R>::k(0));
@@ -227,8 +225,6 @@ __device__ __forceinline__ void pipe_row_filter(const f32x2 (&v)[PipeGeom<W, H, 
         const f32x2 ra = pk(lo_of(s0), lo_of(s1)), rb = pk(hi_of(s0), hi_of(s1));
         *reinterpret_cast<f32x2 *>(t0 + o) = ra;
         *reinterpret_cast<f32x2 *>(t1 + o) = rb;
-        if (top) *reinterpret_cast<f32x2 *>(h0 + o) = ra;
-        if (bot) *reinterpret_cast<f32x2 *>(h1 + o) = rb;
     }
 }
 
@@ -239,10 +235,16 @@ __device__ __forceinline__ void pipe_col_pass(const float *T, Emit emit)
     using G = PipeGeom<W, H, R, NT>;
     constexpr int RS = G::RS;
     const int c = threadIdx.x % G::CP, ys = threadIdx.x / G::CP;
-    const float *base = T + (ys * RS) * G::ST + 2 * c;
     f32x2 t[RS + 2 * R];
+    const float *col = T + 2 * c;
+    const int m0 = ys * RS - R;  // map row of t[0]; only the first / last segment reaches outside the map
 #pragma unroll
-    for (int i = 0; i < RS + 2 * R; ++i) t[i] = *reinterpret_cast<const f32x2 *>(base + i * G::ST);
+    for (int i = 0; i < RS + 2 * R; ++i) {
+        int m = m0 + i;
+        if (i < R) m = m < 0 ? -m : m;                                   // reflect-101 above row 0
+        if (i >= RS + R) m = m > H - 1 ? 2 * (H - 1) - m : m;            // and below row H-1
+        t[i] = *reinterpret_cast<const f32x2 *>(col + m * G::ST);
+    }
 #pragma unroll
     for (int o = 0; o < RS; ++o) {
         f32x2 s = ffma2p(t[o + R], Taps<R>::k(R), pk(0.f, 0.f));
@@ -257,10 +259,13 @@ template <int W, int H, int R, int NT>
 __device__ __forceinline__ float pipe_col_at(const float *T, int y, int x)
 {
     using G = PipeGeom<W, H, R, NT>;
-    const float *q = T + (y + R) * G::ST + x;
-    float s = fmaf(q[0], Taps<R>::k(R), 0.0f);
+    const float *q = T + x;
+    float s = fmaf(q[y * G::ST], Taps<R>::k(R), 0.0f);
 #pragma unroll
-    for (int i = 1; i <= R; ++i) s = fmaf(__fadd_rn(q[i * G::ST], q[-i * G::ST]), Taps<R>::k(R + i), s);
+    for (int i = 1; i <= R; ++i) {
+        const int a = y + i > H - 1 ? 2 * (H - 1) - (y + i) : y + i, b = y - i < 0 ? i - y : y - i;
+        s = fmaf(__fadd_rn(q[a * G::ST], q[b * G::ST]), Taps<R>::k(R + i), s);
+    }
     return s;
 }
 
