@@ -249,14 +249,19 @@ def _cpu_inputs(cfg_id, seed, n):
 
 
 def _cpu_pass(st):
-    """One worker = one core: the reference's per-person path over the worker's persons; seconds."""
+    """One worker = one core: the reference's per-person path over the worker's persons;
+    (seconds, seconds per stage -- the four stages SURVEY 8d asks to be timed separately)."""
     from oracle import np_port as P
     cfg, n, c, s, r, imgs, js, vis = (st[k] for k in ("cfg", "n", "c", "s", "r", "imgs", "js", "vis"))
     (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
     trip = cfg.target_type == "offset"
-    t0 = time.perf_counter()
+    pc = time.perf_counter
+    st_s = {"warpAffine": 0.0, "generate_target": 0.0, "flip_back+average": 0.0, "get_final_preds": 0.0}
+    t0 = pc()
     for i in range(n):  # encode: one person per __getitem__ call
+        a = pc()
         P.crop_person(imgs[i % 2], float(r[i]), c[i], s[i], W, H)
+        b = pc()
         j = js[i].copy()
         j[:, 0:2] = P.map_joints(j[:, 0:2], float(r[i]), c[i], s[i], W, H)
         if cfg.target_type == "gaussian":
@@ -265,13 +270,21 @@ def _cpu_pass(st):
             P.target_offset(j, vis[i], W, H, w, h, cfg.kpd)
         else:
             P.labels_rsn(j, vis[i, :, 0], W, H, w, h)
+        e = pc()
+        st_s["warpAffine"] += b - a
+        st_s["generate_target"] += e - b
     bs = 32  # decode: per validation batch, as validate() does
     with np.errstate(all="ignore"):
         for lo in range(0, n, bs):
+            a = pc()
             avg = P.unflip_average(st["out"][lo:lo + bs], st["fl"][lo:lo + bs], cfg.flip_pairs, trip)
+            b = pc()
             P.final_preds(avg, c[lo:lo + bs], s[lo:lo + bs], "offset" if trip else "gaussian",
                           cfg.kpd, cfg.post_process, cfg.pre_div)
-    return time.perf_counter() - t0
+            e = pc()
+            st_s["flip_back+average"] += b - a
+            st_s["get_final_preds"] += e - b
+    return pc() - t0, st_s
 
 
 def _cpu_worker_main(conn, cfg_id, seed, n):
@@ -316,17 +329,19 @@ class CpuArm:
 def _cpu_calibrate(cfg_id):
     """persons/s of one core, from 8 persons run in this process."""
     st = _cpu_inputs(cfg_id, 1, 8)
-    return 8 / _cpu_pass(st)
+    return 8 / _cpu_pass(st)[0]
 
 
 def _cpu_record(cfg_id, arm, times):
     """times: list (steps) of lists (workers) of seconds."""
     n = arm.per_worker * arm.cores
-    busy = [max(t) for t in times]
+    busy = [max(x[0] for x in t) for t in times]
     rate = n * len(times) / sum(busy)
-    core_rate = float(np.mean([arm.per_worker / x for t in times for x in t]))
+    core_rate = float(np.mean([arm.per_worker / x[0] for t in times for x in t]))
+    stage_us = {k: round(1e6 * float(np.mean([x[1][k] for t in times for x in t])) / arm.per_worker, 1)
+                for k in times[0][0][1]}
     return {"value": rate, "unit": UNIT, "cores": arm.cores, "kind": "port",
-            "per_core": core_rate, "per_worker": arm.per_worker,
+            "per_core": core_rate, "per_worker": arm.per_worker, "stage_us_per_person_per_core": stage_us,
             "sample": "%d step(s) of %d persons (%d per core x %d single-threaded processes) of the same cfg-%d "
                       "encode+decode pass with oracle/np_port.py (numpy+cv2 restatement of the "
                       "reference, checked against its golden vectors); value = persons / slowest worker's "
