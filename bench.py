@@ -398,7 +398,7 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------
 # our arm
 # ----------------------------------------------------------------------------------------
-def link_ceiling(torch, up_bytes, down_bytes, persons):
+def link_ceiling(torch, up_bytes, down_bytes, persons, sync=None):
     """What the host link alone allows: pinned H2D and D2H copies of one chunk's bytes, both
     directions at once on two streams, no kernels (same probe as profiles/pcie_probe.py)."""
     hu, hd = torch.empty(up_bytes, dtype=torch.uint8).pin_memory(), torch.empty(down_bytes, dtype=torch.uint8).pin_memory()
@@ -413,7 +413,9 @@ def link_ceiling(torch, up_bytes, down_bytes, persons):
             hd.copy_(dd, non_blocking=True)
     both()
     torch.cuda.synchronize()
-    reps = 6
+    if sync:
+        sync()  # all ranks start copying together (pinning the buffers takes a different time on each)
+    reps = 40   # ~0.3 s: long against any residual skew between the ranks
     t0 = time.perf_counter()
     for _ in range(reps):
         both()
@@ -661,7 +663,7 @@ def run_ours(args):
                "launches": pipe.launches}
         # what the host links alone allow, all ranks copying at the same time (no kernels)
         barrier()
-        link = link_ceiling(torch, hb.h2d_bytes() // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk)
+        link = link_ceiling(torch, hb.h2d_bytes() // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk, barrier)
         lt = torch.tensor([link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"]], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(lt, op=dist.ReduceOp.SUM)
