@@ -50,7 +50,10 @@ int udp_warp_matrices(const void *center, const void *scale, int cs_f64, const d
  *     Images whose stride is a multiple of 16 bytes are fetched by the TMA unit (one tensor load
  *     per 32 x {32,16,8} output tile, hardware zero fill outside the image); any other stride /
  *     alignment works through a cp.async path.  udp_warp_affine_launches() = kernel launches
- *     one call makes for this crop size (2 when both paths are armed, else 1). */
+ *     one call makes for this crop size (2 when both paths are armed, else 1).  When both are armed the
+ *     cp.async launch runs on a library-owned side stream forked from and joined back into `stream`
+ *     (created once per device on first use; UDP_CROP_FORK=0 in the environment disables the fork) --
+ *     ordering with respect to `stream` is unchanged. */
 int udp_warp_affine_u8(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                        const int32_t *src_stride, const float *M, uint8_t *dst, int W, int H,
                        int N, void *stream);

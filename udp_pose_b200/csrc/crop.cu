@@ -802,6 +802,34 @@ extern "C" int udp_warp_affine_launches(int W, int H)
     return crop_tiles_ok(W, H) && crop_tma_armed(&tmpl) ? 2 : 1;
 }
 
+struct CropFork {
+    cudaStream_t side = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    std::mutex mu;
+    bool ok = false, tried = false;
+};
+static bool crop_fork_enabled()
+{
+    const char *e = getenv("UDP_CROP_FORK");  // UDP_CROP_FORK=0: both launches on the caller's stream
+    return !(e && e[0] == '0');
+}
+static CropFork *crop_fork_get()
+{
+    static CropFork forks[64];
+    static std::mutex init_mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    CropFork &f = forks[dev];
+    std::lock_guard<std::mutex> lock(init_mu);
+    if (!f.tried) {
+        f.tried = true;
+        f.ok = cudaStreamCreateWithFlags(&f.side, cudaStreamNonBlocking) == cudaSuccess &&
+               cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess &&
+               cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming) == cudaSuccess;
+    }
+    return f.ok ? &f : nullptr;
+}
+
 template <class OUT>
 static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                              const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
@@ -810,18 +838,36 @@ static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_
     const int tiles_x = W / udp::CT;
     CUtensorMap tmpl;
     const int tma = crop_tma_armed(&tmpl);
-    if (tma) {  // persons whose images / boxes suit the TMA unit; the launch below does the others
-        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 160 + 16 * tiles_x + 8 * H + 128, stream>>>(
-            tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
-        UDP_LAUNCH_CHECK();
+    // The TMA kernel takes the persons whose images / boxes suit the TMA unit, the cp.async kernel the
+    // others (its CTAs for TMA persons exit at once).  The two touch disjoint persons, so the cp.async
+    // launch goes to a side stream forked from and joined back into the caller's stream (one side
+    // stream and event pair per device, created on first use; 3 % faster than back to back:
+    // 2.28 -> 2.21 ms per 16 384 persons).  UDP_CROP_FORK=0 keeps both on the caller's stream.
+    cudaStream_t tile_stream = stream;
+    CropFork *fk = nullptr;
+    if (tma && crop_fork_enabled() && (fk = crop_fork_get()) != nullptr) {
+        std::lock_guard<std::mutex> lock(fk->mu);  // record + wait must pair up per call
+        cudaEventRecord(fk->fork, stream);
+        cudaStreamWaitEvent(fk->side, fk->fork, 0);
+        tile_stream = fk->side;
     }
     for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
         const int nn = N - n0 < 65535 ? N - n0 : 65535;
         typename OUT::Args a = oargs;
         udp::crop_args_advance(a, (size_t)n0 * person_elems);
-        udp::warp_affine_u8_tile_kernel<OUT><<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, stream>>>(
+        udp::warp_affine_u8_tile_kernel<OUT><<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, tile_stream>>>(
             src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0, a, W, H, tma);
         UDP_LAUNCH_CHECK();
+    }
+    if (tma) {
+        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 160 + 16 * tiles_x + 8 * H + 128, stream>>>(
+            tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
+        UDP_LAUNCH_CHECK();
+    }
+    if (fk) {
+        std::lock_guard<std::mutex> lock(fk->mu);
+        cudaEventRecord(fk->join, fk->side);
+        cudaStreamWaitEvent(stream, fk->join, 0);
     }
     return 0;
 }
