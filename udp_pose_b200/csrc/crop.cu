@@ -169,7 +169,11 @@ constexpr int CT_THREADS = 128;              // 4 warps, 8 tile rows each
 #ifndef UDP_CROP_SMEM_KB
 #define UDP_CROP_SMEM_KB 24
 #endif
-constexpr int CT_SMEM = UDP_CROP_SMEM_KB * 1024;  // footprint buffer (bytes), + 16 bytes slack
+// footprint buffer (bytes), + 16 bytes slack; a template parameter of the tiled kernels.  32 KB (7 CTAs per SM, 0.7 %
+// of the SURVEY 8d boxes miss the TMA box budget instead of 6 %) is 3.7 % faster up to 256x256 crops, 24 KB
+// (8 CTAs per SM) 1 % faster at 384x288 (measured)
+constexpr int CT_SMEM_LARGE_CROP = UDP_CROP_SMEM_KB * 1024;
+constexpr int CT_SMEM_SMALL_CROP = 32 * 1024;
 
 __device__ __forceinline__ void zero_bytes(uint8_t *base, int lo, int hi)
 {
@@ -269,12 +273,12 @@ __device__ __forceinline__ uint32_t crop_tile_finish(const CropTaps &tp)
 #define UDP_CROP_NBOX 2
 #endif
 constexpr int CT_NBOX = UDP_CROP_NBOX;                   // TMA boxes in flight per CTA
-constexpr int CT_BOX = (CT_SMEM / CT_NBOX) & ~127;  // one box
+__host__ __device__ constexpr int ct_box(int smem) { return (smem / CT_NBOX) & ~127; }  // one box
 struct CropPlan {
     int lead, boxw, boxh, tr;
     bool tma;
 };
-__device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw, int ss, const float *m)
+__device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw, int ss, const float *m, int box_bytes)
 {
     CropPlan p;
     p.lead = (int)((uintptr_t)src & 15);
@@ -292,7 +296,7 @@ __device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw
         int boxw = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
         if (!(boxw & 16) && boxw < 512) boxw += 16;  // odd number of 16-byte chunks per row: rotated gathers spread over the banks
         const int boxh = ((ey + 4) >> 10) + 3;
-        if (boxw <= 512 && boxh <= 256 && boxw * boxh <= CT_BOX) {  // 256 two-byte elements per box row at most
+        if (boxw <= 512 && boxh <= 256 && boxw * boxh <= box_bytes) {  // 256 two-byte elements per box row at most
             p.boxw = boxw; p.boxh = boxh; p.tr = tr; p.tma = true;
             break;
         }
@@ -435,7 +439,7 @@ __host__ __device__ inline void crop_args_advance(CropF32Args &a, size_t elems)
 
 // grid = (tile columns, persons); a CTA walks down its tile column, so everything that depends
 // only on the person and the column (matrix, Q10 column deltas, image geometry) is computed once.
-template <class OUT>
+template <class OUT, int CT_SMEM>
 __global__ void __launch_bounds__(CT_THREADS)
 warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                            const int32_t *src_stride, const float *M, typename OUT::Args oargs, int W, int H, int skip_tma)
@@ -454,7 +458,7 @@ warp_affine_u8_tile_kernel(const uint8_t *const *src_ptrs, const int32_t *src_h,
 
     const uint8_t *src = src_ptrs[n];
     const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
-    if (skip_tma && crop_plan(src, sh, sw, ss, m).tma) return;  // the TMA kernel does this person
+    if (skip_tma && crop_plan(src, sh, sw, ss, m, ct_box(CT_SMEM)).tma) return;  // the TMA kernel does this person
     const int ssm = ss & 15;
     // the image buffer as 16-byte chunks: [buf, buf + lim + 16) may be read (images are < 2 GiB)
     const char *buf = reinterpret_cast<const char *>((uintptr_t)src & ~(uintptr_t)15);
@@ -618,7 +622,7 @@ __device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bd
     }
 }
 
-template <class OUT>
+template <class OUT, int CT_SMEM>
 __global__ void __launch_bounds__(CT_THREADS)
 warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_t *const *src_ptrs,
                           const int32_t *src_h, const int32_t *src_w, const int32_t *src_stride,
@@ -638,7 +642,8 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
     const float *m = M + 6 * (size_t)n;
     const uint8_t *src = src_ptrs[n];
     const int sh = src_h[n], sw = src_w[n], ss = src_stride[n];
-    const CropPlan pl = crop_plan(src, sh, sw, ss, m);
+    constexpr int CT_BOX = ct_box(CT_SMEM);
+    const CropPlan pl = crop_plan(src, sh, sw, ss, m, CT_BOX);
     if (!pl.tma) return;
     const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
     const int lead = pl.lead, pitch = pl.boxw, TR = pl.tr;
@@ -830,10 +835,25 @@ static CropFork *crop_fork_get()
     return f.ok ? &f : nullptr;
 }
 
+template <class OUT, int SM>
+static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
+                                const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
+                                size_t person_elems, int W, int H, int N, cudaStream_t stream);
+
 template <class OUT>
 static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                              const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
                              size_t person_elems, int W, int H, int N, cudaStream_t stream)
+{
+    if ((long long)W * H <= 256 * 256)
+        return crop_launch_tiled_sm<OUT, udp::CT_SMEM_SMALL_CROP>(src_ptrs, src_h, src_w, src_stride, M, oargs, person_elems, W, H, N, stream);
+    return crop_launch_tiled_sm<OUT, udp::CT_SMEM_LARGE_CROP>(src_ptrs, src_h, src_w, src_stride, M, oargs, person_elems, W, H, N, stream);
+}
+
+template <class OUT, int SM>
+static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
+                                const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
+                                size_t person_elems, int W, int H, int N, cudaStream_t stream)
 {
     const int tiles_x = W / udp::CT;
     CUtensorMap tmpl;
@@ -855,12 +875,12 @@ static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_
         const int nn = N - n0 < 65535 ? N - n0 : 65535;
         typename OUT::Args a = oargs;
         udp::crop_args_advance(a, (size_t)n0 * person_elems);
-        udp::warp_affine_u8_tile_kernel<OUT><<<dim3(tiles_x, nn), udp::CT_THREADS, udp::CT_SMEM + 16 + 8 * H, tile_stream>>>(
+        udp::warp_affine_u8_tile_kernel<OUT, SM><<<dim3(tiles_x, nn), udp::CT_THREADS, SM + 16 + 8 * H, tile_stream>>>(
             src_ptrs + n0, src_h + n0, src_w + n0, src_stride + n0, M + 6 * (size_t)n0, a, W, H, tma);
         UDP_LAUNCH_CHECK();
     }
     if (tma) {
-        udp::warp_affine_u8_tma_kernel<OUT><<<N, udp::CT_THREADS, udp::CT_SMEM + 160 + 16 * tiles_x + 8 * H + 128, stream>>>(
+        udp::warp_affine_u8_tma_kernel<OUT, SM><<<N, udp::CT_THREADS, SM + 160 + 16 * tiles_x + 8 * H + 128, stream>>>(
             tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
         UDP_LAUNCH_CHECK();
     }
