@@ -169,11 +169,14 @@ constexpr int CT_THREADS = 128;              // 4 warps, 8 tile rows each
 #ifndef UDP_CROP_SMEM_KB
 #define UDP_CROP_SMEM_KB 24
 #endif
-// footprint buffer (bytes), + 16 bytes slack; a template parameter of the tiled kernels.  32 KB (7 CTAs per SM, 0.7 %
+// footprint buffer (bytes), + 16 bytes slack; a template parameter of the tiled kernels.  34 KB (6 CTAs per SM, 0.5 %
 // of the SURVEY 8d boxes miss the TMA box budget instead of 6 %) is 3.7 % faster up to 256x256 crops, 24 KB
 // (8 CTAs per SM) 1 % faster at 384x288 (measured)
 constexpr int CT_SMEM_LARGE_CROP = UDP_CROP_SMEM_KB * 1024;
-constexpr int CT_SMEM_SMALL_CROP = 32 * 1024;
+#ifndef UDP_CROP_SMEM_SMALL_KB
+#define UDP_CROP_SMEM_SMALL_KB 34
+#endif
+constexpr int CT_SMEM_SMALL_CROP = UDP_CROP_SMEM_SMALL_KB * 1024;
 
 __device__ __forceinline__ void zero_bytes(uint8_t *base, int lo, int hi)
 {
