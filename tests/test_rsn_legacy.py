@@ -81,3 +81,19 @@ def test_product_tap_tables_match_cv2():
     from udp_pose_b200 import device_api as D
     for n in (5, 7, 9, 11, 13, 15):
         assert np.array_equal(D.cv_gauss_taps_f64(n), cv2.getGaussianKernel(n, 0, cv2.CV_64F).ravel())
+
+
+@pytest.mark.gpu
+def test_device_get_results_unaligned_input_takes_scalar_loads():
+    """A network output that does not start on a 16-byte boundary goes through the scalar staging loop
+    (the float4 loop needs aligned maps); same results."""
+    import torch
+    from udp_pose_b200 import device_api as D
+    N, K, osh, ish, ksz, _ = G.CASES["coco_k5"]
+    out, c, s = G.inputs("coco_k5")
+    buf = torch.empty(out.size + 1, dtype=torch.float32, device="cuda")
+    view = buf[1:].view(*out.shape)
+    view.copy_(torch.from_numpy(out))
+    assert view.data_ptr() % 16 != 0
+    preds, maxvals = D.rsn_get_results(view, c, s, ish, ksz)
+    _check("coco_k5", preds.cpu().numpy(), maxvals.cpu().numpy())
