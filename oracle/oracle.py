@@ -63,6 +63,23 @@ def rotate_points(joints_xy, rot_deg, center, scale, W, H, do_clip=False):
     return out
 
 
+def fliplr_joints(joints, joints_vis, width, pairs, mul_vis=True):
+    """a4: deep_hrnet/lib/utils/transforms.py:50-64 (mul_vis=True: returns joints*joints_vis, every column
+    multiplied, :64) and RSN/lib/utils/transforms.py:70-79 (`flip_joints`, mul_vis=False: no product).
+    x = width - x - 1 (two float64 subtractions, :55), then the rows of every pair swapped in both arrays
+    (:58-62).  joints, joints_vis float64 [N,K,3] -> new arrays (the reference works in place); width
+    scalar or [N].  Pinned by tests/golden/fliplr.npz (outputs of the reference's two functions)."""
+    j = np.array(joints, np.float64, copy=True)
+    v = np.array(joints_vis, np.float64, copy=True)
+    N = j.shape[0]
+    wd = np.broadcast_to(np.asarray(width, np.float64), (N,))
+    j[..., 0] = wd[:, None] - j[..., 0] - 1
+    for a, b in pairs:
+        j[:, [a, b]] = j[:, [b, a]]
+        v[:, [a, b]] = v[:, [b, a]]
+    return (j * v if mul_vis else j), v
+
+
 def accuracy_pck(output, target, thr=0.5):
     """accuracy(output, target, 'gaussian', thr) of deep_hrnet/lib/core/evaluate.py:41-71
     (calc_dists :16-28, dist_acc :31-38), restated with array operations in the same dtypes:

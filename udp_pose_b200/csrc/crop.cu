@@ -17,6 +17,7 @@
 #include <cmath>
 #include <cstring>
 #include <mutex>
+#include <type_traits>
 
 #include "decode_pipe.cuh"
 #include "tma_host.cuh"
@@ -234,18 +235,42 @@ __device__ __forceinline__ uint32_t crop_tile_pixel(int X, int Y, int pitch, int
 
 // The same pixel in two halves, so that a caller can put the loads of the next row in front of
 // the arithmetic of the current one (uniform 16-byte phase only: pitch % 16 == 0).
+#ifndef UDP_CROP_PRED3
+#define UDP_CROP_PRED3 1
+#endif
+#ifndef UDP_CROP_AXIS
+#define UDP_CROP_AXIS 1
+#endif
+#ifndef UDP_CROP_LARGE_MINB
+#define UDP_CROP_LARGE_MINB 6
+#endif
+#ifndef UDP_CROP_PITCHSEL
+#define UDP_CROP_PITCHSEL 1
+#endif
 struct CropTaps {
-    uint32_t u0, u1, u2, v0, v1, v2, h0, fxy;
+    uint32_t u0, u1, u2, v0, v1, v2, h0, W0, W1;
 };
 __device__ __forceinline__ CropTaps crop_tile_load(int X, int Y, int pitch, int K0)
 {
     CropTaps tp;
     const int sx = X >> 10, sy = Y >> 10;
-    tp.fxy = (((uint32_t)X >> 5) & 31u) | (((uint32_t)Y << 11) & 0x1f0000u);  // fx | fy << 16
+    const uint32_t fx = ((uint32_t)X >> 5) & 31u, fy = ((uint32_t)Y >> 5) & 31u;
+    const uint32_t wxp = fx * 0xffffu + 32u;  // (32 - fx) | fx << 16
+    tp.W1 = fy * wxp;                         // (wy * wx0 | wy * wx1 << 16), each <= 1024
+    tp.W0 = wxp * 32u - tp.W1;
     const int a0 = sy * pitch + (3 * sx + K0);
     const unsigned q0 = (unsigned)a0 & ~3u, q1 = q0 + (unsigned)pitch;  // pitch % 4 == 0: both rows share the byte phase
-    tp.u0 = lds_u32(q0); tp.u1 = lds_u32(q0 + 4); tp.u2 = lds_u32(q0 + 8);
-    tp.v0 = lds_u32(q1); tp.v1 = lds_u32(q1 + 4); tp.v2 = lds_u32(q1 + 8);
+    tp.u0 = lds_u32(q0); tp.u1 = lds_u32(q0 + 4);
+    tp.v0 = lds_u32(q1); tp.v1 = lds_u32(q1 + 4);
+#if UDP_CROP_PRED3
+    // the six bytes of a row reach into the third word only at byte phase 3 (a quarter of the lanes): the
+    // other lanes stay out of that load, which then costs about one wavefront instead of two or three.
+    // (Their u2 / v2 keep whatever the registers held: only bytes the funnel shift never selects.)
+    asm volatile("{\n.reg .pred p;\nsetp.eq.u32 p, %2, 3;\n@p ld.shared.u32 %0, [%3+8];\n@p ld.shared.u32 %1, [%4+8];\n}"
+                 : "+r"(tp.u2), "+r"(tp.v2) : "r"((unsigned)a0 & 3u), "r"(q0), "r"(q1));
+#else
+    tp.u2 = lds_u32(q0 + 8); tp.v2 = lds_u32(q1 + 8);
+#endif
     tp.h0 = (uint32_t)a0 << 3;
     return tp;
 }
@@ -256,12 +281,9 @@ __device__ __forceinline__ uint32_t crop_tile_finish(const CropTaps &tp)
     const uint32_t c_r = __byte_perm(lo0, lo1, 0x7430);  // [r00 r01 r10 r11]
     const uint32_t c_t = __byte_perm(lo0, hi0, 0x5241);  // [g00 g01 b00 b01]
     const uint32_t c_b = __byte_perm(lo1, hi1, 0x5241);  // [g10 g11 b10 b11]
-    const uint32_t fx = tp.fxy & 0xffffu, fy = tp.fxy >> 16;
-    const uint32_t wxp = fx * 0xffffu + 32u;             // (32 - fx) | fx << 16
-    const uint32_t W0 = (32u - fy) * wxp, W1 = fy * wxp; // (wy*wx0 | wy*wx1 << 16), each <= 1024
-    const uint32_t Sr = __dp2a_hi(W1, c_r, __dp2a_lo(W0, c_r, 512u));
-    const uint32_t Sg = __dp2a_lo(W1, c_b, __dp2a_lo(W0, c_t, 512u));
-    const uint32_t Sb = __dp2a_hi(W1, c_b, __dp2a_hi(W0, c_t, 512u));
+    const uint32_t Sr = __dp2a_hi(tp.W1, c_r, __dp2a_lo(tp.W0, c_r, 512u));
+    const uint32_t Sg = __dp2a_lo(tp.W1, c_b, __dp2a_lo(tp.W0, c_t, 512u));
+    const uint32_t Sb = __dp2a_hi(tp.W1, c_b, __dp2a_hi(tp.W0, c_t, 512u));
     return __byte_perm(__byte_perm(Sr << 6, Sg << 6, 0x4462), Sb << 6, 0x4610);
 }
 
@@ -277,16 +299,22 @@ __device__ __forceinline__ uint32_t crop_tile_finish(const CropTaps &tp)
 #endif
 constexpr int CT_NBOX = UDP_CROP_NBOX;                   // TMA boxes in flight per CTA
 __host__ __device__ constexpr int ct_box(int smem) { return (smem / CT_NBOX) & ~127; }  // one box
+// bytes between the boxes and colc[]: 128 (descriptor) + 8 * CT_NBOX (mbarriers) + 8 (pitch) + 8 * CT_NBOX (cring), 16-aligned
+constexpr int CT_TAIL = (128 + 8 * CT_NBOX + 8 + 8 * CT_NBOX + 15) & ~15;
 struct CropPlan {
-    int lead, boxw, boxh, tr;
-    bool tma;
+    int lead, boxw, boxh, tr, boxw_min;
+    bool tma, axis;
 };
+// axis: no rotation (every evaluation-time box, 40 % of the training-time ones): the source column depends
+// on the output column only and the source row on the output row only -- see crop_gather_axis.
+__device__ __forceinline__ bool crop_axis_aligned(const float *m) { return m[1] == 0.0f && m[3] == 0.0f; }
 __device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw, int ss, const float *m, int box_bytes)
 {
     CropPlan p;
     p.lead = (int)((uintptr_t)src & 15);
-    p.boxw = p.boxh = p.tr = 0;
+    p.boxw = p.boxh = p.tr = p.boxw_min = 0;
     p.tma = false;
+    p.axis = crop_axis_aligned(m);
     const double a00 = fabs((double)m[0]) * 1024.0, a01 = fabs((double)m[1]) * 1024.0;
     const double a10 = fabs((double)m[3]) * 1024.0, a11 = fabs((double)m[4]) * 1024.0;
     // (also NaN) tame coefficients only: Q10 coordinates stay far from int32 overflow, boxes below 256
@@ -296,11 +324,14 @@ __device__ __forceinline__ CropPlan crop_plan(const uint8_t *src, int sh, int sw
 #pragma unroll
     for (int tr = CT; tr >= 8; tr >>= 1) {
         const int ex = (int)(a00 * 31.0 + a01 * (double)(tr - 1)), ey = (int)(a10 * 31.0 + a11 * (double)(tr - 1));
-        int boxw = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
-        if (!(boxw & 16) && boxw < 512) boxw += 16;  // odd number of 16-byte chunks per row: rotated gathers spread over the banks
+        const int bmin = (3 * (((ex + 4) >> 10) + 3) + 15 + 15) & ~15;  // + 15: the box starts on a 16-byte boundary
         const int boxh = ((ey + 4) >> 10) + 3;
-        if (boxw <= 512 && boxh <= 256 && boxw * boxh <= box_bytes) {  // 256 two-byte elements per box row at most
-            p.boxw = boxw; p.boxh = boxh; p.tr = tr; p.tma = true;
+        if (bmin <= 512 && boxh <= 256 && bmin * boxh <= box_bytes) {  // 256 two-byte elements per box row at most
+            int boxw = bmin;
+            // rotated gathers walk across the rows of the box: an odd number of 16-byte chunks per row spreads
+            // them over the banks (the default; the TMA kernel may pick another width, crop_pick_pitch)
+            if (!p.axis && !(boxw & 16) && boxw + 16 <= 512 && (boxw + 16) * boxh <= box_bytes) boxw += 16;
+            p.boxw = boxw; p.boxw_min = bmin; p.boxh = boxh; p.tr = tr; p.tma = true;
             break;
         }
     }
@@ -333,29 +364,40 @@ struct CropU8Args {
 struct CropOutU8 {
     using Args = CropU8Args;
     static constexpr bool ROW_MAJOR = UDP_CROP_U8_ROWMAJOR;
+    static constexpr bool IS_F32 = false;
     uint8_t *base, *p;
     size_t row_bytes, step;
-    int p0;
     uint32_t osel;
     bool act;
     __device__ __forceinline__ void init(const Args &a, int n, int W, int H, int lane)
     {
-        // per-lane constants of the 96-byte row repack: word `lane` holds bytes 4*lane .. 4*lane+3
-        p0 = min((4 * lane) / 3, 30);
-        osel = (lane % 3 == 0) ? 0x4210u : ((lane % 3 == 1) ? 0x5421u : 0x6542u);
-        asm volatile("" : "+r"(p0), "+r"(osel));  // keep them in registers (ptxas rematerialised them per pixel)
+        // A warp's row of 32 pixels is 96 bytes = 24 aligned words.  Word j starts inside pixel floor(4j/3):
+        // pixels 0, 1, 2 of every group of four hold the first byte of one word each (at byte 0, 1, 2 of the
+        // pixel), pixel 3 of none.  So lane l (l % 4 != 3) fetches its right neighbour's pixel with ONE
+        // shuffle, cuts word j = l - l/4 out of the two and stores it: 24 lanes, 96 contiguous bytes.
+        osel = (lane % 4 == 0) ? 0x4210u : ((lane % 4 == 1) ? 0x5421u : 0x6542u);
+        asm volatile("" : "+r"(osel));  // keep it in a register (ptxas rematerialised it per pixel)
         row_bytes = (size_t)W * 3;
         step = (size_t)(CT_THREADS / 32) * row_bytes;
-        base = a.dst + (size_t)n * H * row_bytes + 4 * lane;
+        base = a.dst + (size_t)n * H * row_bytes + 4 * (lane - lane / 4);
         p = base;
-        act = lane < 24;
+        act = lane % 4 != 3;
     }
-    __device__ __forceinline__ void seek(int y, int x0) { p = base + (size_t)y * row_bytes + (size_t)x0 * 3; }
+    __device__ __forceinline__ void seek(int y, int x0) { p = base + (unsigned)(y * (int)row_bytes + x0 * 3); }
     __device__ __forceinline__ void emit(uint32_t px)
     {
-        const uint32_t PA = __shfl_sync(0xffffffffu, px, p0), PB = __shfl_sync(0xffffffffu, px, p0 + 1);
-        if (act) *reinterpret_cast<uint32_t *>(p) = __byte_perm(PA, PB, osel);
+        const uint32_t nx = __shfl_down_sync(0xffffffffu, px, 1);
+        if (act) *reinterpret_cast<uint32_t *>(p) = __byte_perm(px, nx, osel);
         p += step;
+    }
+    // row i * ROWSTEP below the row of the last seek(); with the crop width known at compile time (WC) the
+    // offset is an immediate of the store (the running 64-bit pointer cost four instructions per row)
+    template <int ROWSTEP, int WC>
+    __device__ __forceinline__ void emit_at(uint32_t px, int i)
+    {
+        const uint32_t nx = __shfl_down_sync(0xffffffffu, px, 1);
+        const size_t off = WC ? (size_t)(i * ROWSTEP * WC * 3) : (size_t)(i * ROWSTEP) * row_bytes;
+        if (act) *reinterpret_cast<uint32_t *>(p + off) = __byte_perm(px, nx, osel);
     }
 };
 
@@ -379,6 +421,7 @@ __device__ __forceinline__ float crop_norm(uint32_t px, int c, float mean, float
 struct CropOutF32 {
     using Args = CropF32Args;
     static constexpr bool ROW_MAJOR = false;
+    static constexpr bool IS_F32 = true;
     float *base, *basef, *p, *pf;
     size_t plane, step;
     int W_;
@@ -402,13 +445,12 @@ struct CropOutF32 {
     }
     __device__ __forceinline__ void seek(int y, int x0)
     {
-        p = base + (size_t)y * W_ + x0;
-        if (basef) pf = basef + (size_t)y * W_ - x0;
+        p = base + (y * W_ + x0);
+        if (basef) pf = basef + (y * W_ - x0);
     }
-    __device__ __forceinline__ void emit(uint32_t px)
+    __device__ __forceinline__ void norm3(uint32_t px, float &v0, float &v1, float &v2) const
     {
-        float v0, v1;
-        const float v2 = crop_norm(px, 2, mean2, sd2, inv2, fast);
+        v2 = crop_norm(px, 2, mean2, sd2, inv2, fast);
         if (fast) {  // the same operations as crop_norm, two channels per instruction
             const float y = 0x1.010102p-8f;
             const f32x2 x = fsub2p(pk(__uint_as_float(__byte_perm(px, 0x4B000000u, 0x7440u)),
@@ -424,12 +466,26 @@ struct CropOutF32 {
             v0 = crop_norm(px, 0, -lo_of(nmean01), -lo_of(nsd01), lo_of(inv01), false);
             v1 = crop_norm(px, 1, -hi_of(nmean01), -hi_of(nsd01), hi_of(inv01), false);
         }
+    }
+    __device__ __forceinline__ void emit(uint32_t px)
+    {
+        float v0, v1, v2;
+        norm3(px, v0, v1, v2);
         __stcs(p, v0); __stcs(p + plane, v1); __stcs(p + 2 * plane, v2);
         p += step;
         if (basef) {
             __stcs(pf, v0); __stcs(pf + plane, v1); __stcs(pf + 2 * plane, v2);
             pf += step;
         }
+    }
+    template <int ROWSTEP, int WC>
+    __device__ __forceinline__ void emit_at(uint32_t px, int i)
+    {
+        float v0, v1, v2;
+        norm3(px, v0, v1, v2);
+        const size_t off = WC ? (size_t)(i * ROWSTEP * WC) : (size_t)(i * ROWSTEP) * W_;
+        __stcs(p + off, v0); __stcs(p + off + plane, v1); __stcs(p + off + 2 * plane, v2);
+        if (basef) { __stcs(pf + off, v0); __stcs(pf + off + plane, v1); __stcs(pf + off + 2 * plane, v2); }
     }
 };
 
@@ -609,7 +665,7 @@ __device__ unsigned int g_tmap_busy[TM_SLOTS];
 
 // ROWS rows (every fourth of a tile) of one warp: the taps of row i+1 are loaded before the
 // arithmetic, shuffles and store of row i.
-template <int ROWS, class OUT>
+template <int ROWS, int WC, class OUT>
 __device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bdx, int pitch, int K0, OUT &out)
 {
     int2 q[ROWS];
@@ -620,26 +676,116 @@ __device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bd
     for (int i = 0; i < ROWS; ++i) {
         CropTaps nxt;
         if (i + 1 < ROWS) nxt = crop_tile_load(q[i + 1].x + adx, q[i + 1].y + bdx, pitch, K0);
-        out.emit(crop_tile_finish(cur));
+        out.template emit_at<CT_THREADS / 32, WC>(crop_tile_finish(cur), i);
         if (i + 1 < ROWS) cur = nxt;
     }
 }
 
-template <class OUT, int CT_SMEM>
-__global__ void __launch_bounds__(CT_THREADS)
+// ---------------------------------------------------------------------------------------
+// Axis-aligned persons (rotation 0: m01 == m10 == 0).  The four weights of a pixel factor into a column
+// part and a row part, S = wy0 * h(sy, x) + wy1 * h(sy + 1, x) with h(r, x) = wx0 * p[r][sx] + wx1 * p[r][sx + 1]
+// (exact integers, so the result is the same bit for bit): sx, wx and with them the byte offset, the byte
+// phase and every selector are constants of the lane, sy and wy are the same for the whole warp.  A warp
+// walks DOWN its rows and keeps h of the last source row: a source row is loaded and blended horizontally
+// once (3 shared loads, the third one only on the lanes at byte phase 3, 2 funnel shifts, 2 PRMT, 3 IDP.2A)
+// however many output rows use it -- 1.7 source rows per output row at the mean scale of the SURVEY 8d
+// boxes instead of 2, and half as many instructions per pixel as the general gather.
+// ---------------------------------------------------------------------------------------
+struct CropHRow {
+    uint32_t r, g, b;
+};
+__device__ __forceinline__ CropHRow crop_axis_hrow(unsigned addr, bool phi3, uint32_t sh8, uint32_t wxp)
+{
+    const uint32_t u0 = lds_u32(addr), u1 = lds_u32(addr + 4);
+    uint32_t u2;  // deliberately not initialised: lanes not at byte phase 3 never select a byte of it
+    asm volatile("{\n.reg .pred p;\nsetp.ne.u32 p, %1, 0;\n@p ld.shared.u32 %0, [%2+8];\n}" : "+r"(u2) : "r"((unsigned)phi3), "r"(addr));
+    const uint32_t lo = __funnelshift_r(u0, u1, sh8), hi = __funnelshift_r(u1, u2, sh8);  // [r0 g0 b0 r1] [g1 b1 . .]
+    const uint32_t c_rg = __byte_perm(lo, hi, 0x4130);  // [r0 r1 g0 g1]
+    const uint32_t c_b = __byte_perm(lo, hi, 0x5252);   // [b0 b1 b0 b1]
+    CropHRow h;
+    h.r = __dp2a_lo(wxp, c_rg, 0u);
+    h.g = __dp2a_hi(wxp, c_rg, 0u);
+    h.b = __dp2a_lo(wxp, c_b, 0u);
+    return h;
+}
+// RW consecutive output rows of one warp.  rq: their Q10 row bases (y component; bdx is 0 for every lane);
+// base: shared address of this lane's first word in source row 0 (the box's rows are `pitch` apart).
+// rq[i] = (byte offset of the top source row from the box origin's row 0, i.e. sy * pitch; Q10 row coordinate).
+template <int RW, int WC, class OUT>
+__device__ __forceinline__ void crop_gather_axis(const int2 *rq, unsigned base, int pitch, bool phi3, uint32_t sh8,
+                                                 uint32_t wxp, OUT &out)
+{
+    int2 qn = rq[0];
+    int cur = qn.x - pitch;  // offset of the source row held in hb
+    CropHRow ht = {0u, 0u, 0u}, hb = {0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < RW; ++i) {
+        const int2 qc = qn;
+        if (i + 1 < RW) qn = rq[i + 1];  // one row ahead (all of them at once cost registers: spills in this loop)
+        const int top = qc.x, bot = top + pitch;
+        if (bot != cur) {  // (equal: enlargement, both rows are already here)
+            if (top == cur) ht = hb;
+            else ht = crop_axis_hrow(base + (unsigned)top, phi3, sh8, wxp);
+            hb = crop_axis_hrow(base + (unsigned)bot, phi3, sh8, wxp);
+            cur = bot;
+        }
+        // (S + 512) >> 10 is byte 2 of 64 * S + 32768, S = (32 - fy) * ht + fy * hb <= 32 * 8160
+        const uint32_t w1 = ((uint32_t)qc.y << 1) & 0x7c0u, w0 = 2048u - w1;  // fy * 64
+        const uint32_t Sr = w1 * hb.r + (w0 * ht.r + 32768u);
+        const uint32_t Sg = w1 * hb.g + (w0 * ht.g + 32768u);
+        const uint32_t Sb = w1 * hb.b + (w0 * ht.b + 32768u);
+        out.template emit_at<1, WC>(__byte_perm(__byte_perm(Sr, Sg, 0x4462), Sb, 0x4610), i);
+    }
+}
+
+// Rotated persons: a warp's 32 taps lie on a slanted line through the box, lane i at (row, byte) =
+// i * (m10, 3 * m00), so which banks they hit depends on the row pitch.  The pitch may be any multiple of 16
+// bytes that still fits the buffer: warp 0 tries them on four sample rows (wavefronts of one load = the
+// largest number of distinct words in one bank; both tap rows and all three words of a row follow the same
+// pattern) and keeps the best.  Offline model over the SURVEY 8d boxes: 2.7 wavefronts per load with the
+// "odd number of chunks" rule, 2.1 with the pick.
+__device__ __forceinline__ int crop_pick_pitch(const CropPlan &pl, const float *m, int box_bytes, int lane)
+{
+    const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
+    const int adx = q10_col(m00, lane), bdx = q10_col(m10, lane);
+    int sx[4], sy[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int y = 9 * k;
+        sx[k] = (q10_row(m01, m02, y) + adx) >> 10;
+        sy[k] = (q10_row(m11, m12, y) + bdx) >> 10;
+    }
+    int best = pl.boxw, best_wf = 1 << 30;
+    for (int pw = pl.boxw_min; pw <= 512 && pw * pl.boxh <= box_bytes && pw < pl.boxw_min + 128; pw += 16) {
+        int wf = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int word = (sy[k] * pw + 3 * sx[k]) >> 2, bank = word & 31;
+            const unsigned mb = __match_any_sync(0xffffffffu, bank), mw = __match_any_sync(0xffffffffu, word);
+            const unsigned leaders = __ballot_sync(0xffffffffu, lane == __ffs(mw) - 1);
+            wf += __reduce_max_sync(0xffffffffu, __popc(mb & leaders));
+        }
+        if (wf < best_wf) { best_wf = wf; best = pw; }
+    }
+    return best;
+}
+
+template <class OUT, int CT_SMEM, int WC>
+__global__ void __launch_bounds__(CT_THREADS, ((CT_SMEM > 30 * 1024) ? 6 : UDP_CROP_LARGE_MINB) - (OUT::IS_F32 ? 1 : 0))  // CTAs per SM: footprint buffers, registers
 warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_t *const *src_ptrs,
                           const int32_t *src_h, const int32_t *src_w, const int32_t *src_stride,
-                          const float *M, typename OUT::Args oargs, int W, int H)
+                          const float *M, typename OUT::Args oargs, int W_, int H)
 {
-    // CT_NBOX boxes of CT_BOX bytes | 128 B descriptor | 32 B of mbarriers | int4 colc[W/32] | int2 rowq[H]
+    const int W = WC ? WC : W_;  // WC: the crop width as a compile-time constant (0: any width)
+    // CT_NBOX boxes of CT_BOX bytes | 128 B descriptor | mbarriers | pitch | int2 cring[CT_NBOX] | int4 colc[W/32] | int2 rowq[H]
     // dynamic shared memory is only guaranteed 16-byte alignment; TMA destinations need 128
     extern __shared__ __align__(16) unsigned char fp_raw[];
     unsigned char *fp = fp_raw + ((128u - ((unsigned)__cvta_generic_to_shared(fp_raw) & 127u)) & 127u);  // still a shared-space pointer
     const unsigned fpa = (unsigned)__cvta_generic_to_shared(fp);
     const unsigned sdesc = fpa + CT_SMEM, mbar = sdesc + 128;
     const int tiles_x = W / CT;
-    int4 *colc = reinterpret_cast<int4 *>(fp + CT_SMEM + 160);  // per tile column: min/max of the Q10 column deltas
-    int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + 160 + 16 * tiles_x);
+    int4 *colc = reinterpret_cast<int4 *>(fp + CT_SMEM + CT_TAIL);  // per tile column: min/max of the Q10 column deltas
+    int2 *rowq = reinterpret_cast<int2 *>(fp + CT_SMEM + CT_TAIL + 16 * tiles_x);
 
     const int n = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const float *m = M + 6 * (size_t)n;
@@ -649,9 +795,21 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
     const CropPlan pl = crop_plan(src, sh, sw, ss, m, CT_BOX);
     if (!pl.tma) return;
     const double m00 = m[0], m01 = m[1], m02 = m[2], m10 = m[3], m11 = m[4], m12 = m[5];
-    const int lead = pl.lead, pitch = pl.boxw, TR = pl.tr;
+    const int lead = pl.lead, TR = pl.tr;
+    const bool axis = UDP_CROP_AXIS && pl.axis;
+    int pitch = pl.boxw;
+    volatile int *pitch_sh = reinterpret_cast<volatile int *>(fp + CT_SMEM + 128 + 8 * CT_NBOX);  // after the mbarriers
+    // corners (first tap column / row) of the tiles whose boxes are in flight, one per box: written by warp 0
+    // when it issues the load, read by everybody once the tile's turn has come
+    int2 *cring = reinterpret_cast<int2 *>(fp + CT_SMEM + 128 + 8 * CT_NBOX + 8);
 
-    for (int y = t; y < H; y += CT_THREADS) rowq[y] = make_int2(q10_row(m01, m02, y), q10_row(m11, m12, y));
+    // Q10 row bases; axis-aligned persons (whose X base is the same for every row: Xc) keep the byte offset
+    // of the row's top source row there instead
+    const int Xc = q10_row(m01, m02, 0);
+    for (int y = t; y < H; y += CT_THREADS) {
+        const int qy = q10_row(m11, m12, y);
+        rowq[y] = make_int2(axis ? (qy >> 10) * pitch : q10_row(m01, m02, y), qy);
+    }
     for (int c = t; c < tiles_x; c += CT_THREADS) {
         const int A0 = q10_col(m00, c * CT), A1 = q10_col(m00, c * CT + CT - 1);
         const int B0 = q10_col(m10, c * CT), B1 = q10_col(m10, c * CT + CT - 1);
@@ -660,6 +818,10 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
     unsigned long long gdesc = 0;
     if (warp == 0) {
         reinterpret_cast<uint32_t *>(fp + CT_SMEM)[lane] = reinterpret_cast<const uint32_t *>(&tmpl)[lane];
+#if UDP_CROP_PITCHSEL
+        if (!pl.axis) pitch = crop_pick_pitch(pl, m, CT_BOX, lane);
+#endif
+        if (lane == 0) *pitch_sh = pitch;
         __syncwarp();
         unsigned slot = 0;
         if (lane == 0) {
@@ -668,7 +830,7 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
             asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"((3 * sw + lead + 1) >> 1) : "memory");
             asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(sh) : "memory");
             asm volatile("tensormap.replace.tile.global_stride.shared::cta.b1024.b64 [%0], 0, %1;" ::"r"(sdesc), "l"((unsigned long long)ss) : "memory");
-            asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pl.boxw >> 1) : "memory");
+            asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"r"(sdesc), "r"(pitch >> 1) : "memory");
             asm volatile("tensormap.replace.tile.box_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"r"(sdesc), "r"(pl.boxh) : "memory");
             slot = atomicAdd(&g_tmap_next, 1u) & (TM_SLOTS - 1);
             while (atomicCAS(&g_tmap_busy[slot], 0u, 1u) != 0u) slot = (slot + 1) & (TM_SLOTS - 1);
@@ -684,88 +846,106 @@ warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
     }
-    __syncthreads();
-
-    OUT out;
-    out.init(oargs, n, W, H, lane);
-    const unsigned tx_bytes = (unsigned)(pl.boxw * pl.boxh);
+    // tile order: down a tile column, then the next column; tile k lives in box k % CT_NBOX and the load cursor
+    // (warp 0 only) runs CT_NBOX - 1 tiles ahead of the gather cursor.
+    __syncthreads();  // rowq, colc, the descriptor, the barriers and the pitch are in place
+    pitch = *pitch_sh;
+    const unsigned tx_bytes = (unsigned)(pitch * pl.boxh);
     const int ntiles = tiles_x * (H / TR);
 
     // tile (cx, y0): first tap column / row of its footprint; the box starts at the 16-byte boundary below
-    auto corner = [&](int cx, int y0) {
-        const int2 qa = rowq[y0], qb = rowq[y0 + TR - 1];
-        const int4 cc = colc[cx];
-        return make_int2((min(qa.x, qb.x) + cc.x) >> 10, (min(qa.y, qb.y) + cc.z) >> 10);
+    auto corner = [&](int cx_, int y0_) {
+        const int2 qa = rowq[y0_], qb = rowq[y0_ + TR - 1];
+        const int4 cc = colc[cx_];
+        return make_int2(((axis ? Xc : min(qa.x, qb.x)) + cc.x) >> 10, (min(qa.y, qb.y) + cc.z) >> 10);
     };
-    auto issue = [&](int2 g, int b) {  // thread 0: arm the barrier of buffer b and start the load
-        const unsigned bar = mbar + 8 * b;
+    auto issue = [&](int2 g_, int b_) {  // one thread: publish the corner, arm the barrier of box b_, start the load
+        const unsigned bar = mbar + 8 * b_;
+        cring[b_] = g_;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tx_bytes) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                     ::"r"(fpa + b * CT_BOX), "l"(gdesc), "r"(((3 * g.x + lead) & ~15) >> 1), "r"(g.y), "r"(bar) : "memory");
+                     ::"r"(fpa + b_ * CT_BOX), "l"(gdesc), "r"(((3 * g_.x + lead) & ~15) >> 1), "r"(g_.y), "r"(bar) : "memory");
     };
-
-    // tile order: down a tile column, then the next column (ROW_MAJOR: across first).  The load
-    // cursor runs CT_NBOX - 1 tiles ahead of the gather cursor; tile k lives in box k % CT_NBOX.
-    auto advance = [&](int &cx_, int &y0_) {
-        if (OUT::ROW_MAJOR) {
-            if (++cx_ == tiles_x) { cx_ = 0; y0_ += TR; }
-        } else {
-            y0_ += TR;
-            if (y0_ >= H) { y0_ = 0; ++cx_; }
-        }
-    };
-    int2 gq[CT_NBOX];  // corners of the tiles in flight (gq[0] = the tile being gathered)
-    int lcx = 0, ly0 = 0, lbox = 0;  // load cursor
+    int lcx = 0, ly0 = 0, lbox = 0;  // load cursor (warp 0)
+    if (warp == 0) {
 #pragma unroll
-    for (int i = 0; i < CT_NBOX - 1; ++i) {
-        gq[i] = make_int2(0, 0);
-        if (i < ntiles) {
-            gq[i] = corner(lcx, ly0);
-            if (t == 0) issue(gq[i], lbox);
-            advance(lcx, ly0);
-            lbox = lbox + 1 == CT_NBOX ? 0 : lbox + 1;
-        }
+        for (int i = 0; i < CT_NBOX - 1; ++i)
+            if (i < ntiles) {
+                const int2 g_ = corner(lcx, ly0);
+                if (lane == 0) issue(g_, lbox);
+                ly0 += TR;
+                if (ly0 >= H) { ly0 = 0; ++lcx; }
+                lbox = lbox + 1 == CT_NBOX ? 0 : lbox + 1;
+            }
     }
+    __syncthreads();  // cring[0 .. CT_NBOX - 2]
+
+    OUT out;
+    out.init(oargs, n, W, H, lane);
+    // not zero-filled by the hardware: bytes [0, lead) of a row (they precede the image) and, when the row has
+    // an odd number of bytes, the second half of its last two-byte element -- neither exists for 16-byte
+    // aligned images of even width (every decoded image of the reference's datasets)
+    const int rowb = 3 * sw + lead;
+    const bool may_fix = lead != 0 || (rowb & 1);
     int cx = 0, y0 = 0, adx = 0, bdx = 0, b = 0;
-    unsigned par = 0;  // parity of box b's current fill
+    int ax_col = 0;          // axis-aligned persons: 3 * sx + lead of this lane's column ...
+    uint32_t ax_wxp = 0;     // ... and its weight pair (32 - fx) | fx << 16
+    unsigned par = 0;        // parity of box b's current fill
     for (int k = 0; k < ntiles; ++k) {
-        const int2 g = gq[0];
-        if (k + CT_NBOX - 1 < ntiles) {  // the box being refilled was released by the barrier that ended tile k-1
-            gq[CT_NBOX - 1] = corner(lcx, ly0);
-            if (t == 0) issue(gq[CT_NBOX - 1], lbox);
-            advance(lcx, ly0);
+        if (warp == 0 && k + CT_NBOX - 1 < ntiles) {  // the box being refilled was released by the barrier that ended tile k-1
+            const int2 g_ = corner(lcx, ly0);
+            if (lane == 0) issue(g_, lbox);
+            ly0 += TR;
+            if (ly0 >= H) { ly0 = 0; ++lcx; }
             lbox = lbox + 1 == CT_NBOX ? 0 : lbox + 1;
         }
-        if (OUT::ROW_MAJOR || y0 == 0) {  // new tile column: this lane's Q10 column deltas, output pointer
+        const int2 g = cring[b];
+        if (y0 == 0) {  // new tile column: this lane's Q10 column deltas
             adx = q10_col(m00, cx * CT + lane);
             bdx = q10_col(m10, cx * CT + lane);
-            out.seek(y0 + warp, cx * CT);
+            if (axis) {
+                const int X = Xc + adx;  // m01 == 0: the same for every row
+                ax_col = 3 * (X >> 10) + lead;
+                ax_wxp = (((uint32_t)X >> 5) & 31u) * 0xffffu + 32u;
+            }
         }
-        const int xb = 3 * g.x + lead, c0 = xb & ~15, shift0 = xb & 15;
+        const int xb = 3 * g.x + lead, c0 = xb & ~15;
         const unsigned box = fpa + b * CT_BOX;
         mbar_wait(mbar + 8 * b, par);
-        // not zero-filled by the hardware: bytes [0, lead) of a row (they precede the image) and,
-        // when the row has an odd number of bytes, the second half of its last two-byte element
-        const int rowb = 3 * sw + lead;
-        const bool fix_l = lead != 0 && c0 <= 0, fix_r = (rowb & 1) && c0 <= rowb && rowb < c0 + pitch;
-        const bool fix = fix_l || fix_r;
-        if (fix) {
-            for (int rr = t; rr < pl.boxh; rr += CT_THREADS)
-                if ((unsigned)(g.y + rr) < (unsigned)sh) {
-                    if (fix_l) zero_bytes(fp + b * CT_BOX + rr * pitch, min(pitch, -c0), min(pitch, lead - c0));
-                    if (fix_r) fp[b * CT_BOX + rr * pitch + (rowb - c0)] = 0;
-                }
-            __syncthreads();
+        bool fix = false;
+        if (may_fix) {
+            const bool fix_l = lead != 0 && c0 <= 0, fix_r = (rowb & 1) && c0 <= rowb && rowb < c0 + pitch;
+            fix = fix_l || fix_r;
+            if (fix) {
+                for (int rr = t; rr < pl.boxh; rr += CT_THREADS)
+                    if ((unsigned)(g.y + rr) < (unsigned)sh) {
+                        if (fix_l) zero_bytes(fp + b * CT_BOX + rr * pitch, min(pitch, -c0), min(pitch, lead - c0));
+                        if (fix_r) fp[b * CT_BOX + rr * pitch + (rowb - c0)] = 0;
+                    }
+                __syncthreads();
+            }
         }
-        const int K0 = (int)box + shift0 - g.y * pitch - 3 * g.x;
-        if (TR == CT) crop_gather_rows<CT / 4>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
-        else if (TR == CT / 2) crop_gather_rows<CT / 8>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
-        else crop_gather_rows<CT / 16>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
+        if (axis) {
+            const int colb = ax_col - c0;  // this lane's byte offset in a box row
+            const unsigned base = box + (unsigned)(colb & ~3) - (unsigned)(g.y * pitch);
+            const bool phi3 = (colb & 3) == 3;
+            const uint32_t sh8 = (uint32_t)colb << 3;
+            const int yw = y0 + warp * (TR >> 2);
+            out.seek(yw, cx * CT);
+            if (TR == CT) crop_gather_axis<CT / 4, WC>(rowq + yw, base, pitch, phi3, sh8, ax_wxp, out);
+            else if (TR == CT / 2) crop_gather_axis<CT / 8, WC>(rowq + yw, base, pitch, phi3, sh8, ax_wxp, out);
+            else crop_gather_axis<CT / 16, WC>(rowq + yw, base, pitch, phi3, sh8, ax_wxp, out);
+        } else {
+            const int K0 = (int)box + (xb - c0) - g.y * pitch - 3 * g.x;
+            out.seek(y0 + warp, cx * CT);
+            if (TR == CT) crop_gather_rows<CT / 4, WC>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
+            else if (TR == CT / 2) crop_gather_rows<CT / 8, WC>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
+            else crop_gather_rows<CT / 16, WC>(rowq + y0 + warp, adx, bdx, pitch, K0, out);
+        }
         if (fix) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes before the next TMA write
         __syncthreads();  // this box may be refilled
-        advance(cx, y0);
-#pragma unroll
-        for (int i = 0; i + 1 < CT_NBOX; ++i) gq[i] = gq[i + 1];
+        y0 += TR;
+        if (y0 >= H) { y0 = 0; ++cx; }
         if (++b == CT_NBOX) { b = 0; par ^= 1u; }
     }
     // every load of this CTA has landed (each tile waited on its barrier): hand the descriptor slot back
@@ -838,22 +1018,32 @@ static CropFork *crop_fork_get()
     return f.ok ? &f : nullptr;
 }
 
-template <class OUT, int SM>
+template <class OUT, int SM, int WC>
 static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                                 const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
                                 size_t person_elems, int W, int H, int N, cudaStream_t stream);
 
+// Footprint buffer by crop shape (measured), and -- for the uint8 crop -- the TMA kernel with the
+// crop width of the reference's configurations (192, 256, 288) as a compile-time constant.
 template <class OUT>
 static int crop_launch_tiled(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                              const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
                              size_t person_elems, int W, int H, int N, cudaStream_t stream)
 {
-    if ((long long)W * H <= 256 * 256)
-        return crop_launch_tiled_sm<OUT, udp::CT_SMEM_SMALL_CROP>(src_ptrs, src_h, src_w, src_stride, M, oargs, person_elems, W, H, N, stream);
-    return crop_launch_tiled_sm<OUT, udp::CT_SMEM_LARGE_CROP>(src_ptrs, src_h, src_w, src_stride, M, oargs, person_elems, W, H, N, stream);
+    constexpr bool U8 = std::is_same<OUT, udp::CropOutU8>::value;
+#define UDP_CROP_GO(SMB, WCV) \
+    return crop_launch_tiled_sm<OUT, SMB, WCV>(src_ptrs, src_h, src_w, src_stride, M, oargs, person_elems, W, H, N, stream)
+    if ((long long)W * H <= 256 * 256) {
+        if (U8 && W == 192) UDP_CROP_GO(udp::CT_SMEM_SMALL_CROP, U8 ? 192 : 0);
+        if (U8 && W == 256) UDP_CROP_GO(udp::CT_SMEM_SMALL_CROP, U8 ? 256 : 0);
+        UDP_CROP_GO(udp::CT_SMEM_SMALL_CROP, 0);
+    }
+    if (U8 && W == 288) UDP_CROP_GO(udp::CT_SMEM_LARGE_CROP, U8 ? 288 : 0);
+    UDP_CROP_GO(udp::CT_SMEM_LARGE_CROP, 0);
+#undef UDP_CROP_GO
 }
 
-template <class OUT, int SM>
+template <class OUT, int SM, int WC>
 static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *src_h, const int32_t *src_w,
                                 const int32_t *src_stride, const float *M, const typename OUT::Args &oargs,
                                 size_t person_elems, int W, int H, int N, cudaStream_t stream)
@@ -883,7 +1073,7 @@ static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *s
         UDP_LAUNCH_CHECK();
     }
     if (tma) {
-        udp::warp_affine_u8_tma_kernel<OUT, SM><<<N, udp::CT_THREADS, SM + 160 + 16 * tiles_x + 8 * H + 128, stream>>>(
+        udp::warp_affine_u8_tma_kernel<OUT, SM, WC><<<N, udp::CT_THREADS, SM + udp::CT_TAIL + 16 * tiles_x + 8 * H + 128, stream>>>(
             tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
         UDP_LAUNCH_CHECK();
     }
