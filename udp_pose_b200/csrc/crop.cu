@@ -383,7 +383,11 @@ struct CropOutU8 {
         p = base;
         act = lane % 4 != 3;
     }
-    __device__ __forceinline__ void seek(int y, int x0) { p = base + (unsigned)(y * (int)row_bytes + x0 * 3); }
+    __device__ __forceinline__ void seek(int y, int x0)
+    {
+        p = base + (unsigned)(y * (int)row_bytes + x0 * 3);
+        asm volatile("" : "+l"(p));  // a register pair for the tile (ptxas re-added the base from the constant bank per row: 2 %)
+    }
     __device__ __forceinline__ void emit(uint32_t px)
     {
         const uint32_t nx = __shfl_down_sync(0xffffffffu, px, 1);

@@ -178,6 +178,16 @@ def _aid_apply(img, cut, hide):
     return _np(t)[0]
 
 
+def _own_aid(obj, cls):
+    """The reference's Cutout / HideAndSeek objects (lib/utils/transforms.py:144-223) carry the same
+    constructor attributes but no draw(): rebuild ours from them (get_batch on a reference dataset)."""
+    if obj is None or obj is False or hasattr(obj, "draw"):
+        return obj or None
+    if cls is Cutout:
+        return Cutout(obj.prob, obj.radius_factor, obj.num_patch)
+    return HideAndSeek(obj.prob, obj.prob_hiding_patches, obj.grid_sizes)
+
+
 def half_body_transform(ds, joints, joints_vis):
     """JointsDataset.half_body_transform (:124-167): host-side box selection from the visible
     upper- or lower-body joints; uses np.random exactly once, like the reference."""
@@ -280,7 +290,7 @@ class JointsDataset(torch.utils.data.Dataset):
     def _augment(self, rec, img):
         """The reference's random draws, in the reference's order (JointsDataset.py:206-224)."""
         joints, joints_vis = rec["joints_3d"], rec["joints_3d_vis"]
-        c, s, r = rec["center"], rec["scale"], 0
+        c, s, r, flip_w = rec["center"], rec["scale"], 0, 0
         if self.is_train:
             if np.sum(joints_vis[:, 0]) > self.num_joints_half_body and np.random.rand() < self.prob_half_body:
                 ch, sh = self.half_body_transform(joints, joints_vis)
@@ -291,10 +301,10 @@ class JointsDataset(torch.utils.data.Dataset):
             r = np.clip(np.random.randn() * rf, -rf * 2, rf * 2) if random.random() <= 0.6 else 0
             if self.flip and random.random() <= 0.5:
                 img = img[:, ::-1, :]
-                joints, joints_vis = fliplr_joints(joints, joints_vis, img.shape[1], self.flip_pairs)
+                flip_w = img.shape[1]  # fliplr_joints (:222) runs on the device for the whole batch, see get_batch
                 c = c.copy()
                 c[0] = img.shape[1] - c[0] - 1
-        return img, joints, joints_vis, c, s, r
+        return img, joints, joints_vis, c, s, r, flip_w
 
     def get_batch(self, indices, images=None, normalize=None, want_flipped=False):
         """Batched __getitem__: returns (input uint8 CUDA [N,H,W,3], target CUDA, target_weight
@@ -304,20 +314,21 @@ class JointsDataset(torch.utils.data.Dataset):
         (SURVEY 8f-1); with want_flipped it is the pair (input, np.flip(input, 3)) that the flip
         test feeds the model (core/function.py:154-155)."""
         W, H = int(self.image_size[0]), int(self.image_size[1])
-        recs, imgs, js, vs, cs, ss, rs = [], [], [], [], [], [], []
-        aid = self.is_train and (self.cutout or self.hide_and_seek)
+        recs, imgs, js, vs, cs, ss, rs, fws = [], [], [], [], [], [], [], []
+        cutout, hide = _own_aid(getattr(self, "cutout", None), Cutout), _own_aid(getattr(self, "hide_and_seek", None), HideAndSeek)
+        aid = self.is_train and (cutout or hide)
         if aid and normalize is not None:
             raise NotImplementedError("AID erases the uint8 crop (JointsDataset.py:230-235): use the uint8 path, then normalise")
         cuts, hides = [], []
         for n, idx in enumerate(indices):
             rec = copy.deepcopy(self.db[idx])
             img = images[n] if images is not None else self._read(rec["image"])
-            img, j, v, c, s, r = self._augment(rec, img)
+            img, j, v, c, s, r, fw = self._augment(rec, img)
             if aid:  # drawn per record, after the warp parameters and in the reference's order (:231-235)
-                cuts.append(self.cutout.draw(H, W) if self.cutout else [])
-                hides.append(self.hide_and_seek.draw(H, W) if self.hide_and_seek else (0, []))
+                cuts.append(cutout.draw(H, W) if cutout else [])
+                hides.append(hide.draw(H, W) if hide else (0, []))
             recs.append(rec); imgs.append(torch.from_numpy(np.ascontiguousarray(img)))
-            js.append(j); vs.append(v); cs.append(c); ss.append(s); rs.append(float(r))
+            js.append(j); vs.append(v); cs.append(c); ss.append(s); rs.append(float(r)); fws.append(fw)
         c, s = _csN(np.stack(cs), np.stack(ss))
         rot = np.asarray(rs, np.float64)
         M = D.warp_matrices(c, s, rot, (W, H))
@@ -327,14 +338,18 @@ class JointsDataset(torch.utils.data.Dataset):
         else:
             inp = D.crop_batch(src, M, (W, H))
             if aid:
-                ell, ne, gs, mask, mg = _aid_pack(cuts if self.cutout else None, hides if self.hide_and_seek else None, len(recs))
+                ell, ne, gs, mask, mg = _aid_pack(cuts if cutout else None, hides if hide else None, len(recs))
                 D.aid_erase(inp, ell, ne, gs, mask, mg)
-        j = np.ascontiguousarray(np.stack(js), np.float64)
-        jd = torch.from_numpy(j).cuda()
+        jd = torch.from_numpy(np.ascontiguousarray(np.stack(js), np.float64)).cuda()
+        vd = torch.from_numpy(np.ascontiguousarray(np.stack(vs), np.float64)).cuda()
+        fws = np.asarray(fws, np.int32)
+        if fws.any():  # the flip branch (:220-224): fliplr_joints of the mirrored records, one launch
+            sel = torch.from_numpy(np.nonzero(fws)[0]).cuda()
+            jf, vf = D.fliplr_joints_batch(jd[sel], vd[sel], torch.from_numpy(fws[fws != 0]), self.flip_pairs, mul_vis=True)
+            jd[sel], vd[sel] = jf, vf
         D.rotate_points_batch(jd, rot, c, s, (W, H), do_clip=False, out=jd)
-        v = np.ascontiguousarray(np.stack(vs), np.float64)
-        target, tw = self.generate_target_batch(jd, v)
-        jh = _np(jd)
+        target, tw = self.generate_target_batch(jd, vd)
+        jh, v = _np(jd), _np(vd)
         metas = []
         for n, rec in enumerate(recs):
             metas.append({"image": rec["image"], "filename": rec.get("filename", ""),
@@ -475,12 +490,14 @@ def accuracy(output, target, hm_type='gaussian', thr=0.5):
     """lib/core/evaluate.py:41-71 -> (acc float64 [K+1], avg_acc, cnt, pred float32 [N,K,2]).
     Accepts numpy arrays (as the reference) or CUDA tensors (skipping the .cpu().numpy() of
     function.py:76-80,187-192); strided [:, ::3] views of the offset mode are gathered on the
-    device side.  Only hm_type='gaussian' defines `pred` in the reference (:51-55)."""
+    device side.  Only hm_type='gaussian' defines `pred` in the reference (:51-55).  As in the reference,
+    `thr` is accepted and ignored: accuracy() never passes it on to dist_acc (:63), whose default 0.5 applies."""
     if hm_type != 'gaussian':
         raise ValueError("accuracy(): the reference defines pred only for hm_type='gaussian' (evaluate.py:51-55)")
     o = output if isinstance(output, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(output, np.float32))
     t = target if isinstance(target, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(target, np.float32))
-    r = D.accuracy_pck(o.contiguous(), t.contiguous(), 1, thr)
+    # evaluate.py:63 calls dist_acc(dists[idx[i]]) without `thr`: the threshold is always dist_acc's default 0.5
+    r = D.accuracy_pck(o.contiguous(), t.contiguous(), 1, 0.5)
     acc = _np(r["acc"])
     return acc, float(_np(r["avg_acc"])[0]) if int(_np(r["cnt"])[0]) else 0, int(_np(r["cnt"])[0]), _np(r["pred"])
 
@@ -576,11 +593,41 @@ def coco_rescore_nms(preds, all_boxes, image_ids, in_vis_thre, oks_thre, soft_nm
     return out_score, kept
 
 
-def install(inference=None, transforms=None, joints_dataset=None, evaluate=None, nms=None):
+def batched_loader(dataset, batch_size, shuffle=False, drop_last=False, sampler=None, normalize=None,
+                   want_flipped=False):
+    """The main-process replacement for `DataLoader(dataset, batch_size, num_workers=WORKERS)` of
+    tools/train.py:145-158 / tools/test.py:122-128: yields (input, target, target_weight, meta) per batch
+    with ONE launch per stage (JointsDataset.get_batch) instead of one __getitem__ per person in worker
+    processes.  `dataset` is a reference_api.JointsDataset or an instance of the reference's own
+    JointsDataset subclasses (COCODataset, MPIIDataset: same attribute names).  input/target/target_weight
+    are CUDA tensors; meta is collated as torch's default_collate would (lists of strings, stacked arrays).
+
+    Why not workers: the per-sample functions need the GPU, the reference starts its workers by fork
+    (WORKERS = 4..24) after the parent has initialised CUDA, and CUDA cannot be re-initialised in a forked
+    child.  Image decoding (cv2.imread) is the only host work left per record."""
+    from torch.utils.data import BatchSampler, RandomSampler, SequentialSampler
+    from torch.utils.data._utils.collate import default_collate
+    if sampler is None:
+        sampler = RandomSampler(dataset) if shuffle else SequentialSampler(dataset)
+    for idx in BatchSampler(sampler, batch_size, drop_last):
+        inp, target, tw, metas = JointsDataset.get_batch(dataset, idx, normalize=normalize, want_flipped=want_flipped)
+        yield inp, target, tw, default_collate(metas)
+
+
+def install(inference=None, transforms=None, joints_dataset=None, evaluate=None, nms=None, per_sample_encode=False):
     """Substitute the CUDA codec into already-imported reference modules
     (lib.core.inference, lib.utils.transforms, lib.dataset.JointsDataset, lib.core.evaluate, and
     lib.nms.nms and/or lib.dataset.coco for oks_nms / soft_oks_nms -- `nms` may be a module or a list).
-    Returns a dict {(module_name, attr): original} so the caller can undo it."""
+    Returns a dict {(module_name, attr): original} so the caller can undo it.
+
+    joints_dataset: by default only ADDS the batched methods (`get_batch`, `generate_target_batch`) to the
+    reference's JointsDataset class -- use them from the main process, e.g. through `batched_loader(ds, B)`.
+    The per-sample functions the reference calls inside __getitem__ (get_warpmatrix, rotate_points,
+    generate_target, and utils.transforms.fliplr_joints) run in DataLoader workers that the reference forks
+    after CUDA is up (tools/test.py:122-128, train.py:145-158); a forked child cannot use CUDA, and one
+    launch per person would be slower than numpy anyway.  per_sample_encode=True rebinds them all the same
+    (debugging, parity checks): the DataLoader must then be built with num_workers=0 or
+    multiprocessing_context='spawn'."""
     saved = {}
 
     def put(mod, name, fn):
@@ -591,18 +638,38 @@ def install(inference=None, transforms=None, joints_dataset=None, evaluate=None,
 
     for nm in ("get_max_preds", "post", "get_final_preds", "transform_preds"):
         put(inference, nm, globals()[nm])
-    for nm in ("flip_back", "flip_back_offset", "fliplr_joints", "transform_preds"):
+    for nm in ("flip_back", "flip_back_offset", "transform_preds"):
         put(transforms, nm, globals()[nm])
+    if per_sample_encode:
+        put(transforms, "fliplr_joints", fliplr_joints)
     put(evaluate, "accuracy", accuracy)
     for mod in (nms if isinstance(nms, (list, tuple)) else [nms]):
         put(mod, "oks_nms", oks_nms)
         put(mod, "soft_oks_nms", soft_oks_nms)
     if joints_dataset is not None:
-        put(joints_dataset, "get_warpmatrix", get_warpmatrix)
-        put(joints_dataset, "rotate_points", rotate_points)
         cls = joints_dataset.JointsDataset
-        saved[(joints_dataset.__name__, "JointsDataset.generate_target")] = cls.generate_target
-        cls.generate_target = JointsDataset.generate_target
-        cls.generate_target_batch = JointsDataset.generate_target_batch
+        for nm in ("get_batch", "generate_target_batch", "_augment", "_read"):
+            saved[(joints_dataset.__name__, "JointsDataset." + nm)] = cls.__dict__.get(nm)
+            setattr(cls, nm, JointsDataset.__dict__[nm])
+        if per_sample_encode:
+            put(joints_dataset, "get_warpmatrix", get_warpmatrix)
+            put(joints_dataset, "rotate_points", rotate_points)
+            put(joints_dataset, "fliplr_joints", fliplr_joints)
+            saved[(joints_dataset.__name__, "JointsDataset.generate_target")] = cls.generate_target
+            cls.generate_target = JointsDataset.generate_target
     return saved
 
+
+def uninstall(saved, modules):
+    """Undo install(): `modules` is the list of module objects that were passed to it."""
+    by_name = {m.__name__: m for m in modules if m is not None}
+    for (mod_name, attr), orig in saved.items():
+        mod = by_name.get(mod_name)
+        if mod is None:
+            continue
+        target, name = (mod.JointsDataset, attr.split(".", 1)[1]) if attr.startswith("JointsDataset.") else (mod, attr)
+        if orig is None:
+            if name in getattr(target, "__dict__", {}):
+                delattr(target, name)
+        else:
+            setattr(target, name, orig)

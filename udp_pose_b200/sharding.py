@@ -64,15 +64,20 @@ def gather_keypoints(local, n_total, group=None, out=None):
     return out[:n_total]
 
 
-def decode_sharded(cfg, out, flipped, center, scale, group=None):
+def decode_sharded(cfg, out, flipped, center, scale, group=None, decode_fn=None):
     """Decode a replicated batch with each rank doing its own block, then gather.
 
     out/flipped/center/scale hold all N persons (CUDA tensors or numpy); returns the full
-    [N,K,3] float32 keypoints (x, y in source-image pixels, maxval) on every rank."""
-    from . import device_api as D
+    [N,K,3] float32 keypoints (x, y in source-image pixels, maxval) on every rank.
+    decode_fn(cfg, out, flipped, center, scale) -> [n,K,3] replaces the CUDA decoder in the
+    CPU (gloo) tests of this host logic; the product path never passes it."""
     rank, ws = world()
     n = out.shape[0]
     lo, hi = shard_range(n, rank, ws)
-    r = D.decode_batch(cfg, out[lo:hi], None if flipped is None else flipped[lo:hi], center[lo:hi],
-                       scale[lo:hi], want_packed=True)
-    return gather_keypoints(r["packed"], n, group)
+    fl = None if flipped is None else flipped[lo:hi]
+    if decode_fn is None:
+        from . import device_api as D
+        packed = D.decode_batch(cfg, out[lo:hi], fl, center[lo:hi], scale[lo:hi], want_packed=True)["packed"]
+    else:
+        packed = decode_fn(cfg, out[lo:hi], fl, center[lo:hi], scale[lo:hi])
+    return gather_keypoints(packed, n, group)
