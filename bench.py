@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fused", action="store_true", help="skip the 8(f)-1 fused crop+normalize timing")
+    ap.add_argument("--no-configs", action="store_true", help="skip the `configs` block (the other BASELINE.json configs)")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the `sweep` block (cfg-5 strong-scaling sweep, 1 Ki .. 1 Mi persons)")
     ap.add_argument("--config", type=int, default=CFG_ID)
     ap.add_argument("--images", type=int, default=N_IMAGES, help="source image pool (SURVEY 8d: 64; 256 exceeds L2)")
     return ap.parse_args()
@@ -172,12 +174,17 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------
 # synthetic workload resident in HBM
 # ----------------------------------------------------------------------------------------
+def cfg_id_of(cfg):
+    from udp_pose_b200.configs import CONFIGS
+    return [k for k, v in CONFIGS.items() if v is cfg][0]
+
+
 def make_device_workload(cfg, B, rank, torch, D):
     """Deterministic per-rank synthetic batch (SURVEY 8d distributions), generated outside
     the timed region.  Heat maps are produced on the device in slices."""
     from udp_pose_b200 import synth
     dev = torch.device("cuda")
-    rng = np.random.default_rng(1000 * CFG_ID + rank)
+    rng = np.random.default_rng(1000 * cfg_id_of(cfg) + rank)
     c, s, r = synth.boxes(cfg, B, rng, rotate=True)
     K = cfg.num_joints
     js = np.zeros((B, K, 3))
@@ -228,8 +235,12 @@ def make_device_workload(cfg, B, rank, torch, D):
 # ----------------------------------------------------------------------------------------
 # CPU baseline: the numpy/cv2 port of the reference path on the host cores
 # ----------------------------------------------------------------------------------------
+CPU_MAP_POOL = 256  # distinct network-output persons per worker (cycled): 1024 persons of cfg-2 maps would be 1.3 GB per core
+
+
 def _cpu_inputs(cfg_id, seed, n):
-    """Seeded inputs of one worker (SURVEY 8d distributions); generated once, outside every timed region."""
+    """Seeded inputs of one worker, the distributions of make_device_workload (60 % rotated boxes,
+    joint visibility 0.8, the N_IMAGES-image source pool); generated once, outside every timed region."""
     os.environ["OMP_NUM_THREADS"] = "1"
     import cv2
     cv2.setNumThreads(1)
@@ -238,13 +249,15 @@ def _cpu_inputs(cfg_id, seed, n):
     cfg = CONFIGS[cfg_id]
     rng = np.random.default_rng(seed)
     c, s, r = synth.boxes(cfg, n, rng, rotate=True)
-    imgs = synth.source_images(2, rng)
+    imgs = synth.source_images(N_IMAGES, rng)
     K = cfg.num_joints
     js = np.zeros((n, K, 3))
     js[..., 0] = c[:, None, 0] + rng.uniform(-0.6, 0.6, (n, K)) * s[:, None, 0] * 200.0
     js[..., 1] = c[:, None, 1] + rng.uniform(-0.6, 0.6, (n, K)) * s[:, None, 1] * 200.0
-    vis = np.ones((n, K, 3))
-    out, fl = synth.heatmaps(cfg, n, rng)
+    v = (rng.uniform(size=(n, K)) < 0.8).astype(np.float64)
+    vis = np.zeros((n, K, 3))
+    vis[..., 0] = vis[..., 1] = v
+    out, fl = synth.heatmaps(cfg, min(n, CPU_MAP_POOL), rng)
     return dict(cfg=cfg, n=n, c=c, s=s, r=r, imgs=imgs, js=js, vis=vis, out=out, fl=fl)
 
 
@@ -260,7 +273,7 @@ def _cpu_pass(st):
     t0 = pc()
     for i in range(n):  # encode: one person per __getitem__ call
         a = pc()
-        P.crop_person(imgs[i % 2], float(r[i]), c[i], s[i], W, H)
+        P.crop_person(imgs[i % len(imgs)], float(r[i]), c[i], s[i], W, H)
         b = pc()
         j = js[i].copy()
         j[:, 0:2] = P.map_joints(j[:, 0:2], float(r[i]), c[i], s[i], W, H)
@@ -275,11 +288,14 @@ def _cpu_pass(st):
         st_s["generate_target"] += e - b
     bs = 32  # decode: per validation batch, as validate() does
     with np.errstate(all="ignore"):
+        pool = st["out"].shape[0]
         for lo in range(0, n, bs):
             a = pc()
-            avg = P.unflip_average(st["out"][lo:lo + bs], st["fl"][lo:lo + bs], cfg.flip_pairs, trip)
+            j0 = lo % pool                      # the worker's map pool, cycled (views: pool % bs == 0, no copy)
+            m = min(bs, n - lo, pool - j0)
+            avg = P.unflip_average(st["out"][j0:j0 + m], st["fl"][j0:j0 + m], cfg.flip_pairs, trip)
             b = pc()
-            P.final_preds(avg, c[lo:lo + bs], s[lo:lo + bs], "offset" if trip else "gaussian",
+            P.final_preds(avg, c[lo:lo + m], s[lo:lo + m], "offset" if trip else "gaussian",
                           cfg.kpd, cfg.post_process, cfg.pre_div)
             e = pc()
             st_s["flip_back+average"] += b - a
@@ -351,7 +367,7 @@ def _cpu_record(cfg_id, arm, times):
 
 def cpu_baseline(cfg_id, seconds):
     """persons/s of the CPU port on all host cores: one warm-up pass, one timed pass of about `seconds`."""
-    per_worker = max(8, min(512, int(seconds * 0.6 * _cpu_calibrate(cfg_id))))
+    per_worker = max(32, min(1024, (int(seconds * 0.6 * _cpu_calibrate(cfg_id)) // 32) * 32))
     arm = CpuArm(cfg_id, per_worker)
     try:
         arm.step()
@@ -360,17 +376,36 @@ def cpu_baseline(cfg_id, seconds):
         arm.close()
 
 
+def config_dict(cfg, B, world):
+    """`config` of the JSON line: the workload definition, identical for both arms."""
+    (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+    return {"workload": cfg.name + ": " + workload_text(cfg), "cfg": cfg_id_of(cfg), "persons_per_gpu_per_step": B,
+            "sharding": "contiguous persons per rank, one all_gather of [B,K,3] keypoints per step",
+            "l2": "inputs larger than L2 (%.1f GB of network outputs per step per GPU; the %d source images, %.0f MB, are the SURVEY 8d pool)"
+                  % (2 * cfg.channels * h * w * 4 * B / 1e9, N_IMAGES, N_IMAGES * 480 * 640 * 3 / 1e6)}
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path (numpy/cv2 port; the Python tree itself cannot
-    travel to the GPU box) on all host cores.  Rank 0 only.  Exactly --warmup untimed and --steps
-    timed steps; a step is one pass of every core over its own bounded sample, sized so that the
-    whole run takes about two minutes."""
+    travel to the GPU box) on all host cores, on the SAME workload definition as our arm (`config` is
+    identical: same config, same input distributions, same persons per step when that fits).  Rank 0 only.
+    Exactly --warmup untimed and --steps timed steps.  A step is one pass of every core over its share of
+    the step's persons; when --gpus * --batch persons per step would push the run past about 2.5 minutes,
+    the step is a bounded sample of them (stated in cpu_baseline.sample)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     from udp_pose_b200.configs import CONFIGS
     cfg = CONFIGS[args.config]
     steps, warm = max(1, args.steps), max(0, args.warmup)
-    per_worker = max(8, min(512, int(120.0 / (steps + warm) * _cpu_calibrate(args.config))))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    full = args.batch * max(1, args.gpus)                       # persons our arm processes per step
+    per_core_rate = 0.7 * _cpu_calibrate(args.config)           # all cores busy: ~0.7 of the single-core rate
+    budget = 150.0 / (steps + warm)                             # seconds per step
+    per_worker = -(-full // cores)
+    bounded = per_worker / per_core_rate > budget
+    if bounded:
+        per_worker = int(budget * per_core_rate)
+    per_worker = max(32, (per_worker // 32) * 32)               # whole validation batches of 32 (function.py)
     arm = CpuArm(args.config, per_worker)
     try:
         for _ in range(warm):
@@ -383,12 +418,14 @@ def run_reference(args):
     rec = _cpu_record(args.config, arm, times)
     v = rec["value"]
     n_step = per_worker * arm.cores
+    rec["sample"] += ("; %d of the %d persons of our arm's step" % (n_step, full)) if bounded or n_step != full else "; the full step"
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
             "steps": steps, "warmup": warm, "ms_per_step": 1e3 * n_step / v, "wall_ms_per_step": 1e3 * wall / steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64/u8",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 maps / f64 joint prologue / u8 crop",
             "data": "synthetic",
-            "config": {"workload": cfg.name + ": " + workload_text(cfg) + " (CPU: numpy/cv2 port of the reference path)", "cfg": args.config,
-                       "persons_per_step": n_step, "note": "CPU arm does not scale with --gpus"},
+            "config": config_dict(cfg, args.batch, max(1, args.gpus)),
+            "sample_persons_per_step": n_step,
+            "note": "CPU arm: numpy/cv2 port of the reference path on %d host cores; it does not scale with --gpus" % arm.cores,
             "cpu_baseline": rec,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -438,6 +475,169 @@ def workload_text(cfg):
     return "crop %dx%d + %s + %s, %dx%dx%d maps" % (H, W, enc, dec, cfg.channels, h, w)
 
 
+class StepBench:
+    """One configuration resident on this rank's GPU: the synthetic workload, the output buffers and the
+    step (warp matrices -> crop -> joint map -> target encode -> flip-fused decode [-> keypoint gather])."""
+
+    def __init__(self, cfg, B, rank, world, torch, dist, D):
+        self.cfg, self.B, self.rank, self.world, self.torch, self.dist, self.D = cfg, B, rank, world, torch, dist, D
+        K = cfg.num_joints
+        (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
+        self.wl = wl = make_device_workload(cfg, B, rank, torch, D)
+        self.src = D.SourceImages(wl["images"], wl["image_index"])
+        self.crop = torch.empty((B, H, W, 3), dtype=torch.uint8, device="cuda")
+        tshape = (B, 5, K, h, w) if cfg.target_type == "rsn" else (B, cfg.channels, h, w)
+        self.target = torch.empty(tshape, dtype=torch.float32, device="cuda")
+        self.gathered = torch.empty((world * B, K, 3), dtype=torch.float32, device="cuda") if world > 1 else None
+        self.j3 = wl["joints"].clone()
+
+    def step(self, e=None):
+        D, wl, cfg = self.D, self.wl, self.cfg
+        if e: e[0].record()
+        M = D.warp_matrices(wl["center"], wl["scale"], wl["rot"], cfg.image_size)
+        if e: e[1].record()
+        D.crop_batch(self.src, M, cfg.image_size, out=self.crop)
+        if e: e[2].record()
+        D.rotate_points_batch(wl["joints"], wl["rot"], wl["center"], wl["scale"], cfg.image_size, out=self.j3)
+        if e: e[3].record()
+        D.encode_batch(cfg, self.j3, wl["vis"], out=self.target)
+        if e: e[4].record()
+        r = D.decode_batch(cfg, wl["out"], wl["flipped"], wl["center"], wl["scale"], want_packed=True)
+        if e: e[5].record()
+        if self.world > 1:  # the one collective of the path: gather the keypoints (SURVEY 8e)
+            self.dist.all_gather_into_tensor(self.gathered, r["packed"])
+        if e: e[6].record()
+        return r
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def measure(self, steps, warmup, local):
+        """`warmup` untimed steps, then exactly `steps` timed ones between barrier + synchronize on both sides;
+        CUDA events per stage; device time = first event of step 0 to last event of the last step, max over
+        ranks; nvidia-smi clocks sampled during the timed region (rank 0)."""
+        torch = self.torch
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 2)] for _ in range(steps)]
+        for _ in range(warmup):
+            self.step()
+        self.barrier()
+        sampler = ClockSampler(local)
+        if self.rank == 0:
+            sampler.start()
+            time.sleep(0.3)
+        self.barrier()
+        t0 = time.time()
+        for i in range(steps):
+            self.step(ev[i])
+        self.barrier()
+        t1 = time.time()
+        clocks = sampler.stop(t0, t1) if self.rank == 0 else None
+        total_ms = ev[0][0].elapsed_time(ev[-1][-1])
+        stage_ms = {nm: sum(e[i].elapsed_time(e[i + 1]) for e in ev) / steps for i, nm in enumerate(STAGES)}
+        stage_ms["gather"] = sum(e[5].elapsed_time(e[6]) for e in ev) / steps
+        tt = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(tt, op=self.dist.ReduceOp.MAX)
+        return {"total_ms": float(tt[0]), "stage_ms": stage_ms, "clocks": clocks, "steps": steps}
+
+    def tables(self, m, peak):
+        """kernels / paths / value of a measure() result."""
+        cfg, B = self.cfg, self.B
+        ab = algorithmic_bytes(cfg, self.wl["src_area"])
+        stage_ms = m["stage_ms"]
+        kern = {}
+        for nm in STAGES:
+            gbs = ab[nm] * B / (stage_ms[nm] * 1e-3) / 1e9
+            kern[nm] = {"ms": round(stage_ms[nm], 4), "bytes_per_person": round(ab[nm], 1),
+                        "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
+        kern["decode"]["survey_bytes_per_person"] = ab["decode_survey"]
+        kern["decode"]["frac_on_survey_bytes"] = round(ab["decode_survey"] * B / (stage_ms["decode"] * 1e-3) / 1e9 / peak, 4)
+        # the north star states its target per PATH: encode = warp + target (four kernels), decode = one kernel
+        enc_st = ["warp_matrices", "crop", "rotate_points", "encode"]
+        enc_ms, enc_b = sum(stage_ms[n] for n in enc_st), sum(ab[n] for n in enc_st)
+        paths = {"encode_path": {"stages": enc_st, "ms": round(enc_ms, 4), "bytes_per_person": round(enc_b, 1),
+                                 "achieved_gbs": round(enc_b * B / (enc_ms * 1e-3) / 1e9, 1)},
+                 "decode_path": {"stages": ["decode"], "ms": kern["decode"]["ms"], "bytes_per_person": kern["decode"]["bytes_per_person"],
+                                 "achieved_gbs": kern["decode"]["achieved_gbs"]}}
+        for v in paths.values():
+            v["frac"] = round(v["achieved_gbs"] / peak, 4)
+        value = self.world * B * m["steps"] / (m["total_ms"] * 1e-3)
+        return kern, paths, value, ab
+
+    def free(self):
+        for k in ("wl", "src", "crop", "target", "gathered", "j3"):
+            setattr(self, k, None)
+        self.torch.cuda.empty_cache()
+
+
+SWEEP_POINTS = [1 << 10, 1 << 12, 1 << 14, 1 << 16, 1 << 18, 1 << 20]
+SWEEP_CHUNK = 1 << 14
+
+
+def run_sweep(sb, local):
+    """BASELINE.json configs[4]: the large-batch sweep, STRONG scaling -- a point is N persons in total, rank r
+    owns the contiguous block of ceil(N/R) (RSN/lib/utils/dataloader.py:88-93), processed as a stream of chunks
+    of at most 16 Ki persons from the resident pool of `sb` (1 Mi persons of network output would be 418 GB; a
+    chunk's 6.8 GB exceed L2, so repeating it warms nothing), keypoints gathered per chunk.  Per point: one
+    warm-up pass, then `reps` timed passes (CUDA events, max over ranks per pass), the MEDIAN reported, clocks
+    sampled over the timed passes."""
+    torch, dist, D, wl, cfg, world, rank = sb.torch, sb.dist, sb.D, sb.wl, sb.cfg, sb.world, sb.rank
+    srcs = {}
+
+    def chunk_pass(m):
+        sl = slice(0, m)
+        M = D.warp_matrices(wl["center"][sl], wl["scale"][sl], wl["rot"][sl], cfg.image_size)
+        D.crop_batch(srcs[m], M, cfg.image_size, out=sb.crop[sl])
+        D.rotate_points_batch(wl["joints"][sl], wl["rot"][sl], wl["center"][sl], wl["scale"][sl], cfg.image_size, out=sb.j3[sl])
+        D.encode_batch(cfg, sb.j3[sl], wl["vis"][sl], out=sb.target[sl])
+        r = D.decode_batch(cfg, wl["out"][sl], wl["flipped"][sl], wl["center"][sl], wl["scale"][sl], want_packed=True)
+        if world > 1:
+            dist.all_gather_into_tensor(sb.gathered[: world * m], r["packed"])
+
+    points = []
+    for N in SWEEP_POINTS:
+        per = -(-N // world)                                   # ceil(N / R): every rank runs the padded block
+        chunks = [SWEEP_CHUNK] * (per // SWEEP_CHUNK) + ([per % SWEEP_CHUNK] if per % SWEEP_CHUNK else [])
+        for m in set(chunks):                                  # per-person image tables: host work, outside the timing
+            if m not in srcs:
+                srcs[m] = D.SourceImages(wl["images"], wl["image_index"][:m])
+        reps = 7 if per <= (1 << 16) else 3
+        ts = []
+        sampler = ClockSampler(local)
+        t0 = t1 = time.time()
+        for rep in range(reps + 1):                            # repetition 0 is the warm-up
+            sb.barrier()
+            if rep == 1:
+                if rank == 0:
+                    sampler.start()
+                    time.sleep(0.25)
+                sb.barrier()
+                t0 = time.time()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for m in chunks:
+                chunk_pass(m)
+            b.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if rep:
+                ts.append(float(t[0]))
+        sb.barrier()
+        t1 = time.time()
+        clocks = sampler.stop(t0, t1) if rank == 0 else None
+        ms = float(np.median(ts))
+        points.append({"persons": N, "persons_per_gpu": per, "chunks_per_gpu": len(chunks), "ms": round(ms, 4),
+                       "ms_min": round(min(ts), 4), "ms_max": round(max(ts), 4), "reps": reps,
+                       "persons_per_s": round(N / (ms * 1e-3)), "clocks": clocks})
+    return {"cfg": cfg_id_of(cfg), "workload": cfg.name, "scaling": "strong", "n_gpus": world,
+            "timing": "CUDA events, max over ranks per pass, median of `reps` passes after one warm-up pass",
+            "points": points}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -458,61 +658,19 @@ def run_ours(args):
     B, K = args.batch, cfg.num_joints
     (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
 
-    wl = make_device_workload(cfg, B, rank, torch, D)
-    src = D.SourceImages(wl["images"], wl["image_index"])
-    crop = torch.empty((B, H, W, 3), dtype=torch.uint8, device="cuda")
-    tshape = (B, 5, K, h, w) if cfg.target_type == "rsn" else (B, cfg.channels, h, w)
-    target = torch.empty(tshape, dtype=torch.float32, device="cuda")
-    gathered = torch.empty((world * B, K, 3), dtype=torch.float32, device="cuda") if world > 1 else None
-    j3 = wl["joints"].clone()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 2)]
-          for _ in range(args.steps)]
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
 
-    def step(e=None):
-        if e: e[0].record()
-        M = D.warp_matrices(wl["center"], wl["scale"], wl["rot"], cfg.image_size)
-        if e: e[1].record()
-        D.crop_batch(src, M, cfg.image_size, out=crop)
-        if e: e[2].record()
-        D.rotate_points_batch(wl["joints"], wl["rot"], wl["center"], wl["scale"], cfg.image_size, out=j3)
-        if e: e[3].record()
-        D.encode_batch(cfg, j3, wl["vis"], out=target)
-        if e: e[4].record()
-        r = D.decode_batch(cfg, wl["out"], wl["flipped"], wl["center"], wl["scale"], want_packed=True)
-        if e: e[5].record()
-        if world > 1:  # the one collective of the path: gather the keypoints
-            dist.all_gather_into_tensor(gathered, r["packed"])
-        if e: e[6].record()
-        return r
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        step()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.3)
-    barrier()
-    t0 = time.time()
-    for i in range(args.steps):
-        step(ev[i])
-    barrier()
-    t1 = time.time()
-    clocks = sampler.stop(t0, t1) if rank == 0 else None
-    step_ms = sum(e[0].elapsed_time(e[-1]) for e in ev)  # device time of the K steps, this rank
-    # device time from the first event of step 0 to the last event of the last step
-    total_ms = ev[0][0].elapsed_time(ev[-1][-1])
-    stage_ms = {nm: sum(e[i].elapsed_time(e[i + 1]) for e in ev) / args.steps for i, nm in enumerate(STAGES)}
-    stage_ms["gather"] = sum(e[5].elapsed_time(e[6]) for e in ev) / args.steps
-    tt = torch.tensor([total_ms, step_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    total_ms = float(tt[0])
+    sb = StepBench(cfg, B, rank, world, torch, dist, D)
+    wl, src, barrier = sb.wl, sb.src, sb.barrier
+    head = sb.measure(args.steps, max(3, args.warmup), local)
+    total_ms, stage_ms, clocks = head["total_ms"], head["stage_ms"], head["clocks"]
+    target = sb.target
 
     # ---- SURVEY 8(f)-1 (outside the timed step): crop + ToTensor + Normalize + mirrored input, one gather
     fused = None
@@ -578,7 +736,7 @@ def run_ours(args):
                   "persons_per_s": round(nb_l / (lg_ms * 1e-3)),
                   "achieved_gbs": round((cfg.channels * h * w * 4.0 + 16 + 24 * cfg.channels) * nb_l / (lg_ms * 1e-3) / 1e9, 1),
                   "note": "udp_rsn_get_results (RSN/exps/RSN18.coco/test.py:25-71): float64 blur of the zero-padded map + top-2 arg-max, "
-                          "issue-bound (77 % issue-active, DRAM 3 %), no HBM roofline claimed"}
+                          "issue-bound, no HBM roofline claimed"}
     else:
         legacy = None
 
@@ -610,21 +768,25 @@ def run_ours(args):
         nms["note"] = ("udp_coco_rescore + udp_oks_nms (coco.py:321-356, nms.py:75-180), in_vis_thre 0.2, oks_thre 0.9, up to 32 persons "
                        "per image; sequential greedy picks per image, float64 exp: latency/FP64-bound, 232 B per person, no HBM roofline")
 
+    kern, paths, value, ab = sb.tables(head, peak)
+    host = wl["host"]
+    out_head, fl_head = wl["out"][:args.e2e_batch].clone(), wl["flipped"][:args.e2e_batch].clone()
+    sb.free()
+    del wl, src, target
+    torch.cuda.empty_cache()
+
     # ---- end to end through host buffers (pinned), H2D and D2H inside the timed region
     e2e = None
     if not args.no_e2e:
-        del target, crop
-        torch.cuda.empty_cache()
         nb = args.e2e_batch
         hb = HostBatch(cfg, nb, N_IMAGES)
-        hs = wl["host"]
-        hb.images.copy_(torch.from_numpy(hs["images"]))
+        hb.images.copy_(torch.from_numpy(host["images"]))
         hb.image_index[:] = np.arange(nb) % N_IMAGES
         for dst, key in ((hb.center, "center"), (hb.scale, "scale"), (hb.rot, "rot"),
                          (hb.joints, "joints"), (hb.joints_vis, "vis")):
-            dst.copy_(torch.from_numpy(hs[key][:nb]))
-        hb.out.copy_(wl["out"][:nb])
-        hb.out_flipped.copy_(wl["flipped"][:nb])
+            dst.copy_(torch.from_numpy(host[key][:nb]))
+        hb.out.copy_(out_head)
+        hb.out_flipped.copy_(fl_head)
         pipe = HostPipeline(cfg, args.e2e_chunk, N_IMAGES)
         for _ in range(3):
             pipe.run(hb)
@@ -664,64 +826,74 @@ def run_ours(args):
         # what the host links alone allow, all ranks copying at the same time (no kernels)
         barrier()
         link = link_ceiling(torch, hb.h2d_bytes() // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk, barrier)
-        lt = torch.tensor([link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"]], dtype=torch.float64, device="cuda")
+        mine = [link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"]]
+        lt = torch.tensor(mine, dtype=torch.float64, device="cuda")
         if world > 1:
+            allr = [torch.empty_like(lt) for _ in range(world)]
+            dist.all_gather(allr, lt)
+            link["per_rank"] = [{"h2d_gbs": round(float(v[0]), 1), "d2h_gbs": round(float(v[1]), 1),
+                                 "ceiling_persons_per_s": round(float(v[2]), 1)} for v in allr]
             dist.all_reduce(lt, op=dist.ReduceOp.SUM)
-            link["note"] += "; summed over the %d ranks, which copy concurrently" % world
+            link["note"] += "; summed over the %d ranks, which copy concurrently (per_rank: each rank's own figures)" % world
         link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"] = (round(float(v), 1) for v in lt)
         e2e["link"] = link
+        del hb, pipe
+    del out_head, fl_head
+    torch.cuda.empty_cache()
+
+    # ---- the other BASELINE.json configs, same step, same batch, own clock record each
+    cfg_block, sweep = None, None
+    if not args.no_configs:
+        cfg_block = []
+        for cid in sorted(CONFIGS):
+            if cid == args.config:
+                continue
+            o = StepBench(CONFIGS[cid], B, rank, world, torch, dist, D)
+            m = o.measure(max(3, min(args.steps, 10)), 3, local)
+            k2, p2, v2, _ = o.tables(m, peak)
+            cfg_block.append({"cfg": cid, "workload": CONFIGS[cid].name + ": " + workload_text(CONFIGS[cid]),
+                              "persons_per_gpu_per_step": B, "steps": m["steps"], "ms_per_step": round(m["total_ms"] / m["steps"], 4),
+                              "value": round(v2, 1), "kernels": {n: {"ms": k2[n]["ms"], "frac": k2[n]["frac"], "achieved_gbs": k2[n]["achieved_gbs"]} for n in STAGES},
+                              "encode_path_frac": p2["encode_path"]["frac"], "decode_path_frac": p2["decode_path"]["frac"],
+                              "gather_ms": round(m["stage_ms"]["gather"], 4), "clocks": m["clocks"]})
+            if cid == SWEEP_CFG and not args.no_sweep and B >= SWEEP_CHUNK:  # the sweep draws its chunks from this pool
+                sweep = run_sweep(o, local)
+            o.free()
+            del o
+    if sweep is None and not args.no_sweep:
+        o = StepBench(CONFIGS[SWEEP_CFG], SWEEP_CHUNK, rank, world, torch, dist, D)
+        sweep = run_sweep(o, local)
+        o.free()
+        del o
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    ab = algorithmic_bytes(cfg, wl["src_area"])
-    kern = {}
-    for nm in STAGES:
-        gbs = ab[nm] * B / (stage_ms[nm] * 1e-3) / 1e9
-        kern[nm] = {"ms": round(stage_ms[nm], 4), "bytes_per_person": round(ab[nm], 1),
-                    "achieved_gbs": round(gbs, 1), "frac": round(gbs / peak, 4)}
-    kern["decode"]["survey_bytes_per_person"] = ab["decode_survey"]
-    kern["decode"]["frac_on_survey_bytes"] = round(ab["decode_survey"] * B / (stage_ms["decode"] * 1e-3) / 1e9 / peak, 4)
     dom = max(STAGES, key=lambda n: stage_ms[n])
-    # the north star states its target per PATH: encode = warp + target (four kernels), decode = one kernel
-    enc_st = ["warp_matrices", "crop", "rotate_points", "encode"]
-    enc_ms, enc_b = sum(stage_ms[n] for n in enc_st), sum(ab[n] for n in enc_st)
-    paths = {"encode_path": {"stages": enc_st, "ms": round(enc_ms, 4), "bytes_per_person": round(enc_b, 1),
-                             "achieved_gbs": round(enc_b * B / (enc_ms * 1e-3) / 1e9, 1)},
-             "decode_path": {"stages": ["decode"], "ms": kern["decode"]["ms"], "bytes_per_person": kern["decode"]["bytes_per_person"],
-                             "achieved_gbs": kern["decode"]["achieved_gbs"]}}
-    for v in paths.values():
-        v["frac"] = round(v["achieved_gbs"] / peak, 4)
-    # measured DRAM bytes of one launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, committed in
-    # profiles/traffic.json for this config and batch; scaled linearly to another batch size)
-    traffic = None
+    # measured DRAM bytes of one launch (ncu dram__bytes_read.sum + dram__bytes_write.sum), committed in
+    # profiles/traffic.json by profiles/make_traffic.py together with a hash of the kernel sources it was captured
+    # from: used only if that hash is the tree's (a stale capture reads as null), scaled linearly to the batch size
+    traffic, traffic_note = None, "no capture for this configuration"
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tj["cfg%d" % args.config][dom] * B / tj["persons"]
+        if tj.get("source_sha16") != kernel_source_sha16():
+            traffic_note = "profiles/traffic.json was captured from other kernel sources (stale): not used"
+        else:
+            traffic = tj["cfg%d" % args.config][dom] * B / tj["persons"]
+            traffic_note = tj.get("note", "")
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": peak,
-                "unit": "GB/s", "frac": kern[dom]["frac"], "traffic": traffic, "peak_source": peak_src,
+                "unit": "GB/s", "frac": kern[dom]["frac"], "traffic": traffic, "traffic_note": traffic_note, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": ab[dom] * B,
-                "note": "crop reads hit L2 (64-image source pool), so DRAM traffic is below the algorithmic bytes; "
-                        "the kernel is bound by the shared-memory data pipe of the gather (86 % of peak LSU wavefronts, 79 % issue-active), see DESIGN.md"}
-    value = world * B * args.steps / (total_ms * 1e-3)
+                "note": "slowest stage of the step; per-stage figures under `kernels`, per-path under `paths` (DESIGN.md section 4 says what bounds each kernel)"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 maps / f64 joint prologue / u8 crop", "data": "synthetic",
-            "config": {"workload": cfg.name + ": " + workload_text(cfg),
-                       "cfg": args.config, "persons_per_gpu_per_step": B, "sharding": "contiguous persons per rank, one all_gather of [B,K,3] keypoints per step",
-                       "l2": "inputs larger than L2 (%.1f GB of network outputs per step per GPU; the %d source images, %.0f MB, are the SURVEY 8d pool)" % (2 * cfg.channels * h * w * 4 * B / 1e9, N_IMAGES, N_IMAGES * 480 * 640 * 3 / 1e6)},
+            "config": config_dict(cfg, B, world),
             "roofline": roofline, "kernels": kern, "paths": paths,
             "gather_ms": round(stage_ms["gather"], 4),
             "gpu_launches": (len(STAGES) - 1 + D.crop_launches(cfg.image_size)) * args.steps,
@@ -740,11 +912,29 @@ def run_ours(args):
         line.setdefault("next", {})["rsn_get_results"] = legacy
     if e2e:
         line["e2e"] = e2e
+    if cfg_block is not None:
+        line["configs"] = cfg_block
+    if sweep is not None:
+        line["sweep"] = sweep
     if not args.no_cpu and world == 1:
         line["cpu_baseline"] = cpu_baseline(args.config, args.cpu_seconds)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+SWEEP_CFG = 5
+
+
+def kernel_source_sha16():
+    """sha256 (first 16 hex digits) over the CUDA sources and headers the library is built from."""
+    import hashlib
+    from udp_pose_b200 import build as B
+    hs = hashlib.sha256()
+    for f in sorted(B.SOURCES + B.HEADERS):
+        with open(os.path.join(B.CSRC, f), "rb") as fh:
+            hs.update(fh.read())
+    return hs.hexdigest()[:16]
 
 
 if __name__ == "__main__":

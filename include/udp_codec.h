@@ -13,7 +13,13 @@
  *    otherwise) -- any tensor that starts an allocation is;
  *  - `stream` is a cudaStream_t (NULL = default stream); calls are asynchronous;
  *  - return value: 0 on success, otherwise a cudaError_t (> 0) or UDP_EINVAL (< 0);
- *    no exceptions cross the ABI, nothing is allocated, nothing is synchronised;
+ *    no exceptions cross the ABI; no entry point allocates device memory per call or synchronises
+ *    with the host.  Library-owned state, all of it created once per device on first use and
+ *    documented at the entry points that use it: udp_warp_affine_u8 / udp_warp_affine_normalize_f32
+ *    keep one side stream + event pair (the cp.async kernel for the few persons the TMA kernel
+ *    cannot take runs there, forked from and joined back into `stream`; not used while `stream` is
+ *    being captured) and claim slots of a static 8192-entry tensor-map pool in global memory;
+ *    the TMA paths fetch cuTensorMapEncodeTiled from the driver once;
  *  - `cs_f64`: dtype of the center/scale arrays -- 1 = float64 (MPII records,
  *    lib/dataset/mpii.py:55-56), 0 = float32 (COCO records, lib/dataset/coco.py:223-227).
  *    The reference's arithmetic depends on that dtype (numpy promotion), so it is part of
@@ -193,10 +199,11 @@ int udp_rsn_get_results(const float *outputs, const float *outputs_flipped, cons
  *     point applies the drawn parameters:
  *     ellipses [N,max_ellipses,4] float64 (cx, cy, rx, ry; :205-206), n_ellipses [N] int32 (0 = Cutout not
  *     applied to this person), max_ellipses <= 8; either may be NULL (no Cutout).
- *     grid_size [N] int32 (0 = HideAndSeek not applied / grid 0) and hide_mask [N,8] uint32: bit c of the
- *     256-bit mask = cell c hidden, cells numbered in the reference's draw order (outer range(0, width, g),
+ *     grid_size [N] int32 (0 = HideAndSeek not applied / grid 0) and hide_mask [N,UDP_AID_MASK_WORDS] uint32: bit c of
+ *     the 512-bit mask = cell c hidden, cells numbered in the reference's draw order (outer range(0, width, g),
  *     inner range(0, height, g)); either may be NULL.  min_grid = smallest non-zero grid size in use
  *     (cells must fit the mask).  The reference's transposed slice img[x:x_end, y:y_end] (:175) is kept. */
+#define UDP_AID_MASK_WORDS 16
 int udp_aid_erase(uint8_t *img, int N, int H, int W, const double *ellipses, const int32_t *n_ellipses,
                   int max_ellipses, const int32_t *grid_size, const uint32_t *hide_mask, int min_grid,
                   void *stream);

@@ -64,3 +64,36 @@ def test_device_erase_batch_both():
     for k in range(24):
         want = O.aid_erase(O.aid_erase(imgs[k], ellipses=cuts[k]), grid=hides[k][0], hidden=hides[k][1])
         assert np.array_equal(got[k], want), k
+
+
+@pytest.mark.gpu
+def test_device_hide_and_seek_on_the_384x288_crop_with_the_default_grids():
+    """grid 16 on a 384x288 crop has 18 * 24 = 432 cells, more than the old 256-bit mask
+    (one draw in four raised ValueError where the reference works).  The mask now holds 512 cells."""
+    import torch
+    from udp_pose_b200 import device_api as D, reference_api as R
+    np.random.seed(21)
+    hide = R.HideAndSeek(1.0, 0.5, (16, 16, 0))   # always grid 16 (the last size is never drawn)
+    imgs = np.stack([G.image(384, 288, 700 + k) for k in range(6)])
+    hides = [hide.draw(384, 288) for _ in range(6)]
+    assert all(g == 16 and len(bits) == 432 for g, bits in hides)
+    t = torch.from_numpy(imgs.copy()).cuda()
+    D.aid_erase(t, *R._aid_pack(None, hides, 6))
+    got = t.cpu().numpy()
+    for k in range(6):
+        assert np.array_equal(got[k], O.aid_erase(imgs[k], grid=16, hidden=hides[k][1])), k
+
+
+def test_hide_and_seek_grid_that_cannot_fit_fails_at_construction():
+    """... and a combination that cannot fit raises when the dataset is built, not at a random draw."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("reference_api needs the built library's package import only; constructed on the GPU box")
+    from udp_pose_b200 import reference_api as R
+    from udp_pose_b200.configs import CONFIGS
+    c = CONFIGS[3].as_cfg()
+    c.DATASET.CUTOUT, c.DATASET.HIDE_AND_SEEK = None, [1.0, 0.5, (8, 16, 0)]   # grid 8 on 384x288: 1728 cells
+    with pytest.raises(ValueError):
+        R.JointsDataset(c, "", "train", True)
+    c.DATASET.HIDE_AND_SEEK = [1.0, 0.5, (0, 16, 32, 44, 56)]                  # the reference's defaults fit
+    R.JointsDataset(c, "", "train", True)

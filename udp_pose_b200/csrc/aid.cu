@@ -17,7 +17,7 @@
 namespace udp {
 
 constexpr int AID_THREADS = 256;
-constexpr int AID_MASK_WORDS = 8;   // up to 256 cells
+constexpr int AID_MASK_WORDS = UDP_AID_MASK_WORDS;   // up to 512 cells: a 384x288 crop with the reference's smallest grid (16) has 18 * 24 = 432
 
 __global__ void __launch_bounds__(AID_THREADS)
 aid_erase_kernel(uint8_t *__restrict__ img, int H, int W, const double *__restrict__ ellipses,
@@ -64,7 +64,7 @@ extern "C" int udp_aid_erase(uint8_t *img, int N, int H, int W, const double *el
     if (N < 0 || H < 1 || W < 1 || max_ellipses < 0 || max_ellipses > 8) return UDP_EINVAL;
     if (N == 0) return 0;
     if (!img || (n_ellipses && !ellipses) || (grid_size && !hide_mask)) return UDP_EINVAL;
-    if (grid_size) {  // min_grid: the smallest non-zero grid size in use; its cells must fit the 256-bit mask
+    if (grid_size) {  // min_grid: the smallest non-zero grid size in use; its cells must fit the 512-bit mask
         if (min_grid < 1) return UDP_EINVAL;
         const long long cells = (long long)((W + min_grid - 1) / min_grid) * ((H + min_grid - 1) / min_grid);
         if (cells > 32 * udp::AID_MASK_WORDS) return UDP_EINVAL;

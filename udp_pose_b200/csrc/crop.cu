@@ -1063,10 +1063,18 @@ static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *s
     cudaStream_t tile_stream = stream;
     CropFork *fk = nullptr;
     if (tma && crop_fork_enabled() && (fk = crop_fork_get()) != nullptr) {
+        // No fork while the caller's stream is being captured: the shared side stream would join that capture,
+        // and a concurrent plain call from another thread would then be illegal.  If the fork cannot be set up,
+        // both kernels simply run on the caller's stream.
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
         std::lock_guard<std::mutex> lock(fk->mu);  // record + wait must pair up per call
-        cudaEventRecord(fk->fork, stream);
-        cudaStreamWaitEvent(fk->side, fk->fork, 0);
-        tile_stream = fk->side;
+        if (cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone &&
+            cudaEventRecord(fk->fork, stream) == cudaSuccess && cudaStreamWaitEvent(fk->side, fk->fork, 0) == cudaSuccess) {
+            tile_stream = fk->side;
+        } else {
+            (void)cudaGetLastError();
+            fk = nullptr;
+        }
     }
     for (int n0 = 0; n0 < N; n0 += 65535) {  // gridDim.y limit
         const int nn = N - n0 < 65535 ? N - n0 : 65535;
@@ -1081,10 +1089,14 @@ static int crop_launch_tiled_sm(const uint8_t *const *src_ptrs, const int32_t *s
             tmpl, src_ptrs, src_h, src_w, src_stride, M, oargs, W, H);
         UDP_LAUNCH_CHECK();
     }
-    if (fk) {
+    if (fk) {  // the caller's stream must not run ahead of the side stream's kernel: a failed join is an error
         std::lock_guard<std::mutex> lock(fk->mu);
-        cudaEventRecord(fk->join, fk->side);
-        cudaStreamWaitEvent(stream, fk->join, 0);
+        cudaError_t e = cudaEventRecord(fk->join, fk->side);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, fk->join, 0);
+        if (e != cudaSuccess) {
+            cudaStreamSynchronize(fk->side);  // last resort: order by blocking
+            return (int)e;
+        }
     }
     return 0;
 }

@@ -483,10 +483,13 @@ def rsn_get_results(outputs, centers, scales, input_shape, kernel=11, shift=0.25
     return preds, maxvals
 
 
+AID_MASK_WORDS = 16  # UDP_AID_MASK_WORDS of include/udp_codec.h: 512 cells
+
+
 def aid_erase(crops, ellipses=None, n_ellipses=None, grid_size=None, hide_mask=None, min_grid=0):
     """apply drawn Cutout / HideAndSeek parameters to uint8 CUDA crops [N,H,W,3] IN PLACE
     (lib/utils/transforms.py:144-223 at JointsDataset.py:230-235).  ellipses f64 [N,P,4] (cx, cy, rx, ry),
-    n_ellipses i32 [N]; grid_size i32 [N], hide_mask u32/i32 [N,8] (bit c = cell c in draw order)."""
+    n_ellipses i32 [N]; grid_size i32 [N], hide_mask u32/i32 [N,AID_MASK_WORDS] (bit c = cell c in draw order)."""
     assert crops.is_cuda and crops.dtype == torch.uint8 and crops.dim() == 4 and crops.shape[3] == 3 and crops.is_contiguous()
     N, H, W, _ = crops.shape
     P = 0
@@ -497,7 +500,7 @@ def aid_erase(crops, ellipses=None, n_ellipses=None, grid_size=None, hide_mask=N
     if grid_size is not None:
         grid_size = _dev(grid_size, torch.int32)
         hide_mask = _dev(hide_mask, torch.int32)
-        assert grid_size.shape == (N,) and hide_mask.shape == (N, 8)
+        assert grid_size.shape == (N,) and hide_mask.shape == (N, AID_MASK_WORDS)
     _lib.call("udp_aid_erase", _ptr(crops), int(N), int(H), int(W), _ptr(ellipses), _ptr(n_ellipses), int(P),
               _ptr(grid_size), _ptr(hide_mask), int(min_grid), _stream())
     return crops

@@ -97,6 +97,9 @@ class HostPipeline:
         self.runs = 0
         self.chunks_done = 0
         self.launches = 0
+        # the fills above (jcrop zeros, the image tables) ran on the caller's current stream; run() reads them from
+        # s_run, a non-blocking stream with no dependency on it
+        torch.cuda.current_stream(dev).synchronize()
 
     def _schedule(self, n):
         """(offset, size) of the chunks of one pass.  The first upload has no download to overlap

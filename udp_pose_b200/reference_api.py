@@ -152,11 +152,11 @@ def _aid_pack(cut, hide, n):
             if c:
                 ell[i, :len(c)] = np.asarray(c, np.float64)
     if hide is not None:
-        gs, mask = np.zeros(n, np.int32), np.zeros((n, 8), np.uint32)
+        gs, mask = np.zeros(n, np.int32), np.zeros((n, D.AID_MASK_WORDS), np.uint32)
         for i, (g, bits) in enumerate(hide):
             if g and any(bits):
-                if len(bits) > 256:
-                    raise ValueError("HideAndSeek: more than 256 cells (grid %d)" % g)
+                if len(bits) > 32 * D.AID_MASK_WORDS:
+                    raise ValueError("HideAndSeek: more than %d cells (grid %d)" % (32 * D.AID_MASK_WORDS, g))
                 gs[i] = g
                 for c, b in enumerate(bits):
                     if b:
@@ -236,6 +236,11 @@ class JointsDataset(torch.utils.data.Dataset):
         cc, ch = getattr(ds, "CUTOUT", None), getattr(ds, "HIDE_AND_SEEK", None)
         self.cutout = (Cutout(*cc) if len(cc) == 3 else Cutout()) if cc else None
         self.hide_and_seek = (HideAndSeek(*ch) if len(ch) == 3 else HideAndSeek()) if ch else None
+        if self.hide_and_seek:  # fail here, not at a random draw during training: every grid must fit the device mask
+            W_, H_ = int(cfg.MODEL.IMAGE_SIZE[0]), int(cfg.MODEL.IMAGE_SIZE[1])
+            for g in self.hide_and_seek.grid_sizes[:-1]:  # (the last size is never drawn, transforms.py:163)
+                if g and -(-W_ // g) * -(-H_ // g) > 32 * D.AID_MASK_WORDS:
+                    raise ValueError("HideAndSeek: grid %d on a %dx%d crop has more than %d cells" % (g, H_, W_, 32 * D.AID_MASK_WORDS))
         self.target_type = cfg.MODEL.TARGET_TYPE
         self.image_size = np.array(cfg.MODEL.IMAGE_SIZE)
         self.heatmap_size = np.array(cfg.MODEL.HEATMAP_SIZE)
