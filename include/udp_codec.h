@@ -36,6 +36,7 @@ extern "C" {
 #endif
 
 #define UDP_EINVAL (-1)
+#define UDP_ESCRATCH (-2) /* the request does not fit a library-owned, fixed-size workspace (udp_accuracy_pck_noalloc) */
 #define UDP_MAX_SIGMAS 8
 
 /* Library version (major*10000 + minor*100 + patch) and the SM architecture compiled in. */
@@ -168,6 +169,20 @@ int udp_decode_offset(const float *out, const float *out_flipped, const int32_t 
 int udp_accuracy_pck(const float *output, const float *target, int ch_stride, int K, int w, int h,
                      int N, double thr, float *pred, double *dists, double *acc, double *avg_acc,
                      int32_t *cnt, void *stream);
+
+/* udp_accuracy_pck for callers that cannot allocate -- NO COUNTERPART IN THE REFERENCE; added
+ *     (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ *     Same arguments and results as udp_accuracy_pck minus `dists`: that [K,N] float64 workspace is a static
+ *     device array inside the library of UDP_PCK_NOALLOC_MAX_DISTS doubles (4 MiB, held by every GPU that loads
+ *     the library until exit).  N * K > UDP_PCK_NOALLOC_MAX_DISTS returns UDP_ESCRATCH (-2) and launches nothing.
+ *     Calls no cudaMalloc / cudaFree / allocating routine; its only set-up is one cudaGetSymbolAddress per device.
+ *     Every call shares the workspace (it keeps the previous call's contents; each call overwrites all the K*N
+ *     entries it reads, nothing needs clearing): calls that overlap on the GPU -- different streams with no
+ *     ordering between them -- race on it; calls on one stream, or ordered by events, are safe. */
+#define UDP_PCK_NOALLOC_MAX_DISTS (512 * 1024)
+int udp_accuracy_pck_noalloc(const float *output, const float *target, int ch_stride, int K, int w, int h,
+                             int N, double thr, float *pred, double *acc, double *avg_acc, int32_t *cnt,
+                             void *stream);
 
 /* SURVEY 8(f)-4 (first half)  the demo engines' quarter-offset decoder:
  *     get_final_preds(heatmaps, boxes) of deep_hrnet/tools/infer_utils/decode.py:19-40, with its

@@ -14,6 +14,8 @@
 //   coordinates (:21).  HBM-bound: 2*h*w*4 bytes per (person, joint), read once.
 // Kernel 2 (one CTA, one warp per joint): dist_acc per joint (:31-38) and the average over the
 //   joints that have any valid distance (:60-70), float64, joint order as in the reference.
+#include <mutex>
+
 #include "blur.cuh"
 
 namespace udp {
@@ -178,6 +180,62 @@ extern "C" int udp_accuracy_pck(const float *output, const float *target, int ch
     if ((((uintptr_t)output | (uintptr_t)target) & 15) != 0) return UDP_EINVAL;  // 16-byte vector loads
     const long long maps = (long long)N * K;
     if (maps > 0x7fffffffLL) return UDP_EINVAL;
+    if (maps > 0) {
+        udp::pck_dist_kernel<<<(unsigned)maps, udp::PCK_THREADS, 0, (cudaStream_t)stream>>>(output, target, ch_stride, K, w, h, N,
+                                                                                           pred, dists);
+        UDP_LAUNCH_CHECK();
+    }
+    udp::pck_acc_kernel<<<1, 32 * K, 0, (cudaStream_t)stream>>>(dists, K, N, thr, acc, avg_acc, cnt);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// udp_accuracy_pck without caller-provided scratch (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  The [K,N] float64 `dists` workspace lives in a file-scope device array of
+// UDP_PCK_NOALLOC_MAX_DISTS doubles (4 MiB, resident on every GPU that loads the library until exit).
+// In host code `g_pck_scratch` is only a host-side stand-in for the symbol: its device address is fetched with
+// cudaGetSymbolAddress, once per device with that device current, and that pointer goes to the kernels.
+// Every call shares the array and finds the previous call's contents in it; pck_dist_kernel overwrites every
+// one of the K*N entries pck_acc_kernel reads, so nothing has to start at zero.  Two calls that overlap on the
+// GPU (different streams, no ordering between them) race on it.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_pck_scratch[UDP_PCK_NOALLOC_MAX_DISTS];
+
+static int pck_scratch_ptr(double **out)
+{
+    static double *ptrs[64] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return UDP_EINVAL;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_pck_scratch);  // the address on the CURRENT device
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return UDP_EINVAL;
+        ptrs[dev] = reinterpret_cast<double *>(p);
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+extern "C" int udp_accuracy_pck_noalloc(const float *output, const float *target, int ch_stride, int K, int w, int h,
+                                        int N, double thr, float *pred, double *acc, double *avg_acc, int32_t *cnt,
+                                        void *stream)
+{
+    if (N < 0 || K < 1 || K > 32 || w < 1 || h < 1 || ch_stride < 1 || ((w * h) & 3)) return UDP_EINVAL;
+    if (!acc || !avg_acc || !cnt) return UDP_EINVAL;
+    if (N > 0 && (!output || !target || !pred)) return UDP_EINVAL;
+    if ((((uintptr_t)output | (uintptr_t)target) & 15) != 0) return UDP_EINVAL;  // 16-byte vector loads
+    const long long maps = (long long)N * K;
+    if (maps > (long long)UDP_PCK_NOALLOC_MAX_DISTS) return UDP_ESCRATCH;  // does not fit the built-in workspace
+    double *dists = nullptr;
+    const int rc = pck_scratch_ptr(&dists);
+    if (rc) return rc;
     if (maps > 0) {
         udp::pck_dist_kernel<<<(unsigned)maps, udp::PCK_THREADS, 0, (cudaStream_t)stream>>>(output, target, ch_stride, K, w, h, N,
                                                                                            pred, dists);
