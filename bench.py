@@ -819,13 +819,16 @@ def run_ours(args):
         stream_s = float(tsr[0])
         e2e = {"value": world * nb * e_steps / (float(te[0]) * 1e-3), "unit": UNIT,
                "streaming_value": round(world * nb * e_steps / stream_s, 1),
-               "h2d_bytes_per_step": hb.h2d_bytes(), "d2h_bytes_per_step": hb.d2h_bytes(),
+               "h2d_bytes_per_step": pipe.h2d_bytes(hb), "d2h_bytes_per_step": hb.d2h_bytes(),
+               "h2d_bytes_per_step_full_tensors": hb.h2d_bytes(),
                "persons_per_step_per_gpu": nb, "steps": e_steps, "chunk": args.e2e_chunk,
-               "api": "udp_pose_b200.pipeline.HostPipeline.run (pinned host in -> H2D -> 5 kernels via the C ABI -> D2H: crop, target, target_weight, keypoints)",
+               "api": "udp_pose_b200.pipeline.HostPipeline.run (pinned host in -> H2D -> 5 kernels via the C ABI -> D2H: crop, target, target_weight, keypoints)"
+                      + ("; offset configs upload the classification channels only and the decoder gathers its 7x7 offset windows in place from "
+                         "the caller's pinned buffers (udp_decode_offset_split), counted in h2d_bytes_per_step" if pipe.split else ""),
                "launches": pipe.launches}
         # what the host links alone allow, all ranks copying at the same time (no kernels)
         barrier()
-        link = link_ceiling(torch, hb.h2d_bytes() // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk, barrier)
+        link = link_ceiling(torch, pipe.h2d_bytes(hb) // (nb // args.e2e_chunk), hb.d2h_bytes() // (nb // args.e2e_chunk), args.e2e_chunk, barrier)
         mine = [link["h2d_gbs"], link["d2h_gbs"], link["ceiling_persons_per_s"]]
         lt = torch.tensor(mine, dtype=torch.float64, device="cuda")
         if world > 1:

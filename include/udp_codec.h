@@ -29,6 +29,7 @@
 #ifndef UDP_CODEC_H
 #define UDP_CODEC_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -159,6 +160,26 @@ int udp_decode_offset(const float *out, const float *out_flipped, const int32_t 
                       double kpd, const void *center, const void *scale, int cs_f64, int K, int w,
                       int h, float *preds, float *maxvals, float *preds_in, int32_t *argmax_idx,
                       float *packed, int N, void *stream);
+
+/* a10/a11/a15/a16 with split sources -- the host round trip of lib/core/function.py:151-171,205 made cheaper.
+ *     The voting decoder reads the K classification maps in full but only a 7x7 window of each offset map
+ *     (inference.py:166-167,173-174).  cls_out / cls_flipped: [N,3K,h,w] DEVICE tensors of which only the
+ *     classification channels (0::3) need to hold data; off_out / off_flipped: the same tensors' offset channels
+ *     somewhere else with the same [N,3K,h,w] layout -- typically the caller's pinned HOST buffers as seen from the
+ *     device (udp_host_device_pointer), so that two thirds of the network output never cross the host link.
+ *     Everything else as udp_decode_offset; results are bit-identical. */
+int udp_decode_offset_split(const float *cls_out, const float *cls_flipped, const float *off_out,
+                            const float *off_flipped, const int32_t *flip_perm, double kpd, const void *center,
+                            const void *scale, int cs_f64, int K, int w, int h, float *preds, float *maxvals,
+                            float *preds_in, int32_t *argmax_idx, float *packed, int N, void *stream);
+
+/* Host plumbing for the split call, no kernels (the .cpu().numpy() / .cuda() pairs of function.py:154-169):
+ *     udp_copy2d_async: cudaMemcpy2DAsync of `height` rows of `width` bytes, kind 1 = host to device, 2 = device
+ *     to host (one call moves the K classification maps of a chunk: width = h*w*4, pitches = 3*h*w*4);
+ *     udp_host_device_pointer: the device-side address of a pinned, mapped HOST buffer (cudaHostGetDevicePointer). */
+int udp_copy2d_async(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t height,
+                     int kind, void *stream);
+int udp_host_device_pointer(void *host_ptr, void **device_ptr);
 
 /* SURVEY 8(f)-2  accuracy(output, target, hm_type='gaussian', thr)  deep_hrnet/lib/core/evaluate.py:16-71,
  *     call sites lib/core/function.py:76-80 and :187-192 (offset mode passes the [:, ::3] views:

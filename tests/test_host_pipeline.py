@@ -74,3 +74,60 @@ def test_pipeline_matches_direct_calls(cid):
     pipe.synchronize()
     for a, b in zip(want, got):
         assert torch.equal(a, b)
+
+
+def test_split_offsets_reads_the_windows_from_the_host_buffers_only():
+    """cfg 2, split mode (the default): only the classification channels are uploaded; the decoder gathers its
+    7x7 offset windows from the caller's pinned buffers.  The device copies' offset channels are poisoned with NaN
+    before the run -- if the decoder read them, the coordinates would be NaN.  Both modes equal the direct pass, and
+    the split mode moves about a third of the bytes towards the device."""
+    import torch
+    from udp_pose_b200.pipeline import HostBatch, HostPipeline
+    cfg = CONFIGS[2]
+    rng = np.random.default_rng(77)
+    n, chunk, n_images = 200, 64, 3
+    hb = HostBatch(cfg, n, n_images)
+    _fill(hb, cfg, n, rng, n_images)
+    want = _direct(hb, cfg)
+    got = (hb.crop, hb.target, hb.target_weight, hb.keypoints)
+    for split in (True, False):
+        pipe = HostPipeline(cfg, chunk, n_images, split_offsets=split)
+        assert pipe.split == split
+        for sl in pipe.slots:
+            sl["out"].fill_(float("nan"))
+            sl["fl"].fill_(float("nan"))
+        torch.cuda.synchronize()
+        for t in got:
+            t.fill_(0)
+        pipe.run(hb)
+        for a, b in zip(want, got):
+            assert torch.equal(a, b)
+        assert not torch.isnan(hb.keypoints).any()
+    full, less = hb.h2d_bytes(), HostPipeline(cfg, chunk, n_images).h2d_bytes(hb)
+    img = hb.images.numel()
+    assert (less - img) < 0.36 * (full - img)
+
+
+def test_decode_offset_split_entry_point_with_nan_maps():
+    """udp_decode_offset_split on device tensors: classification channels in one pair of tensors, offsets in another
+    (whose classification channels are poisoned); a map holding NaN takes the generic path, which must use the split
+    sources too.  Bit-identical to udp_decode_offset on the complete tensors."""
+    import torch
+    from udp_pose_b200 import device_api as D
+    cfg = CONFIGS[2]
+    rng = np.random.default_rng(78)
+    N, K = 9, cfg.num_joints
+    out, fl = synth.heatmaps(cfg, N, rng)
+    out[3, 3 * 5, 10, 10] = np.nan          # person 3, joint 5: NaN in the classification map
+    c, s, _ = synth.boxes(cfg, N, rng)
+    o, f = torch.from_numpy(out).cuda(), torch.from_numpy(fl).cuda()
+    want = D.decode_offset(o, c, s, cfg.kpd, f, cfg.flip_pairs, want_idx=True)
+    cls_o, cls_f, off_o, off_f = o.clone(), f.clone(), o.clone(), f.clone()
+    for t in (cls_o, cls_f):
+        t.view(N, K, 3, *t.shape[2:])[:, :, 1:] = float("nan")     # offsets must not be read from here
+    for t in (off_o, off_f):
+        t.view(N, K, 3, *t.shape[2:])[:, :, 0] = float("nan")      # nor classification maps from here
+    got = D.decode_offset(cls_o, c, s, cfg.kpd, cls_f, cfg.flip_pairs, want_idx=True, off_ptrs=(off_o.data_ptr(), off_f.data_ptr()))
+    for k in ("idx", "maxvals", "preds", "preds_in"):
+        a, b = want[k].cpu().numpy(), got[k].cpu().numpy()
+        assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), k

@@ -36,6 +36,10 @@ SIGNATURES = {
                             _vp, _vp, _i, _vp],
     "udp_decode_offset": [_vp, _vp, _vp, _d, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp,
                           _i, _vp],
+    "udp_decode_offset_split": [_vp, _vp, _vp, _vp, _vp, _d, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp,
+                                _i, _vp],
+    "udp_copy2d_async": [_vp, C.c_size_t, _vp, C.c_size_t, C.c_size_t, C.c_size_t, _i, _vp],
+    "udp_host_device_pointer": [_vp, _vp],
     "udp_fliplr_joints": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp],
     "udp_transform_preds": [_vp, _i, _vp, _vp, _i, _i, _i, _vp, _i, _i, _vp],
 }

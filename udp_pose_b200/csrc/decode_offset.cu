@@ -22,6 +22,10 @@ namespace udp {
 
 struct DecodeOffsetArgs {
     const float *out, *out_flipped;
+    // where the 7x7 offset windows are gathered from: the same tensors, or (udp_decode_offset_split) other copies of
+    // them with the same [N,3K,h,w] layout -- e.g. the caller's pinned host buffers, mapped into the device's address
+    // space, when only the classification channels were uploaded
+    const float *off_out, *off_flipped;
     const int32_t *flip_perm;
     float kpd;
     const void *center, *scale;
@@ -47,8 +51,8 @@ __device__ __forceinline__ void offset_finish(const DecodeOffsetArgs &p, long lo
     if (threadIdx.x < 14) {
         const int ch = threadIdx.x / 7, i = threadIdx.x - ch * 7;
         const int yy = reflect101(iy - 3 + i, h);
-        const float *a = src + (size_t)(1 + ch) * hw + (size_t)yy * w;
-        const float *f = fl ? fl + (size_t)(1 + ch) * hw + (size_t)yy * w : nullptr;
+        const float *a = p.off_out + (src - p.out) + (size_t)(1 + ch) * hw + (size_t)yy * w;
+        const float *f = fl ? p.off_flipped + (fl - p.out_flipped) + (size_t)(1 + ch) * hw + (size_t)yy * w : nullptr;
         const float fs = ch == 0 ? -1.0f : 1.0f;  // x offsets change sign under the mirror (:40)
         float v[7];
 #pragma unroll
@@ -152,9 +156,9 @@ __device__ __forceinline__ float offset_row_item(const DecodeOffsetArgs &p, long
     const bool mask = bv > 0.0f;
     const int ix = mask ? bi % w : 0, iy = mask ? bi / w : 0;
     const int yo = reflect101(iy - 3 + i, h) * w;
-    const float *a = p.out + (map * 3 + 1 + ch) * (long long)hw + yo;
+    const float *a = p.off_out + (map * 3 + 1 + ch) * (long long)hw + yo;
     const float *f = p.out_flipped
-                         ? p.out_flipped + (((long long)n * p.K + p.flip_perm[k]) * 3 + 1 + ch) * (long long)hw + yo
+                         ? p.off_flipped + (((long long)n * p.K + p.flip_perm[k]) * 3 + 1 + ch) * (long long)hw + yo
                          : nullptr;
     const float fs = ch == 0 ? -1.0f : 1.0f;  // x offsets change sign under the mirror (:40)
     float v[7];
@@ -596,18 +600,19 @@ decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __g
 
 }  // namespace udp
 
-extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
-                                 const int32_t *flip_perm, double kpd, const void *center,
-                                 const void *scale, int cs_f64, int K, int w, int h, float *preds,
-                                 float *maxvals, float *preds_in, int32_t *argmax_idx, float *packed,
-                                 int N, void *stream)
+static int decode_offset_launch(const float *out, const float *out_flipped, const float *off_out, const float *off_flipped,
+                                const int32_t *flip_perm, double kpd, const void *center,
+                                const void *scale, int cs_f64, int K, int w, int h, float *preds,
+                                float *maxvals, float *preds_in, int32_t *argmax_idx, float *packed,
+                                int N, void *stream)
 {
     if (N < 0 || K < 1 || w < 8 || (w & 3) || h < 8) return UDP_EINVAL;
     if (N == 0) return 0;
     if (!out || !preds || !maxvals || (out_flipped && !flip_perm) || ((center == nullptr) != (scale == nullptr)))
         return UDP_EINVAL;
     if ((((uintptr_t)out | (uintptr_t)out_flipped) & 15) != 0) return UDP_EINVAL;  // 16-byte vector access
-    udp::DecodeOffsetArgs a{out, out_flipped, flip_perm, (float)kpd, center, scale, cs_f64, K, w, h,
+    if (!off_out || (out_flipped && !off_flipped)) return UDP_EINVAL;
+    udp::DecodeOffsetArgs a{out, out_flipped, off_out, off_flipped, flip_perm, (float)kpd, center, scale, cs_f64, K, w, h,
                             preds, maxvals, preds_in, argmax_idx, packed};
     long long maps = (long long)N * K;
     if (maps > 0x7fffffffLL) return UDP_EINVAL;
@@ -682,4 +687,41 @@ extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
     udp::decode_offset_kernel<<<(unsigned)maps, threads, gsmem, (cudaStream_t)stream>>>(a);
     UDP_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int udp_decode_offset(const float *out, const float *out_flipped,
+                                 const int32_t *flip_perm, double kpd, const void *center,
+                                 const void *scale, int cs_f64, int K, int w, int h, float *preds,
+                                 float *maxvals, float *preds_in, int32_t *argmax_idx, float *packed,
+                                 int N, void *stream)
+{
+    return decode_offset_launch(out, out_flipped, out, out_flipped, flip_perm, kpd, center, scale, cs_f64, K, w, h, preds,
+                                maxvals, preds_in, argmax_idx, packed, N, stream);
+}
+
+extern "C" int udp_decode_offset_split(const float *cls_out, const float *cls_flipped, const float *off_out,
+                                       const float *off_flipped, const int32_t *flip_perm, double kpd,
+                                       const void *center, const void *scale, int cs_f64, int K, int w, int h,
+                                       float *preds, float *maxvals, float *preds_in, int32_t *argmax_idx,
+                                       float *packed, int N, void *stream)
+{
+    return decode_offset_launch(cls_out, cls_flipped, off_out, off_flipped, flip_perm, kpd, center, scale, cs_f64, K, w, h,
+                                preds, maxvals, preds_in, argmax_idx, packed, N, stream);
+}
+
+// Host plumbing for the split call (no kernels): a strided 2-D asynchronous copy (cudaMemcpy2DAsync; kind: 1 = host to
+// device, 2 = device to host) and the device-side address of a pinned, mapped host buffer.
+extern "C" int udp_copy2d_async(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t height,
+                                int kind, void *stream)
+{
+    if (!dst || !src || width > dpitch || width > spitch || (kind != 1 && kind != 2)) return UDP_EINVAL;
+    if (width == 0 || height == 0) return 0;
+    return (int)cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height,
+                                  kind == 1 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+}
+
+extern "C" int udp_host_device_pointer(void *host_ptr, void **device_ptr)
+{
+    if (!host_ptr || !device_ptr) return UDP_EINVAL;
+    return (int)cudaHostGetDevicePointer(device_ptr, host_ptr, 0);
 }

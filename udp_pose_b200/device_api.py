@@ -119,6 +119,20 @@ def crop_batch(src, M, image_size, out=None):
     return out
 
 
+def copy2d_async(dst_ptr, dpitch, src_ptr, spitch, width, height, to_device=True):
+    """cudaMemcpy2DAsync on torch's current stream (udp_copy2d_async): `height` rows of `width` bytes."""
+    _lib.call("udp_copy2d_async", C.c_void_p(dst_ptr), int(dpitch), C.c_void_p(src_ptr), int(spitch), int(width),
+              int(height), 1 if to_device else 2, _stream())
+
+
+def host_device_pointer(t):
+    """Device-side address of a pinned (mapped) host tensor; raises if the tensor is not mapped."""
+    assert not t.is_cuda and t.is_pinned()
+    out = C.c_void_p()
+    _lib.call("udp_host_device_pointer", C.c_void_p(t.data_ptr()), C.byref(out))
+    return int(out.value)
+
+
 IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)  # tools/train.py:127-129
 
 
@@ -311,8 +325,10 @@ def decode_gaussian(hm, center, scale, flipped=None, pairs=None, post_process=Tr
 
 
 def decode_offset(out, center, scale, kpd, flipped=None, pairs=None, want_idx=False,
-                  want_packed=False):
-    """a10,a11,a15,a16: fused flip-average + get_final_preds('offset')."""
+                  want_packed=False, off_ptrs=None):
+    """a10,a11,a15,a16: fused flip-average + get_final_preds('offset').
+    off_ptrs = (address of the tensor the offset windows of `out` are gathered from, same for `flipped`):
+    udp_decode_offset_split -- `out` / `flipped` then need to hold the classification channels only."""
     out = _dev(out, _F32)
     N, C3, h, w = out.shape
     K = C3 // 3
@@ -331,8 +347,13 @@ def decode_offset(out, center, scale, kpd, flipped=None, pairs=None, want_idx=Fa
     mv = torch.empty((N, K, 1), dtype=_F32, device=dev)
     idx = torch.empty((N, K), dtype=torch.int32, device=dev) if want_idx else None
     packed = torch.empty((N, K, 3), dtype=_F32, device=dev) if want_packed else None
-    _lib.call("udp_decode_offset", _ptr(out), _ptr(fl), _ptr(perm), float(kpd), _ptr(c), _ptr(s),
-              f64, K, w, h, _ptr(preds), _ptr(mv), _ptr(pin), _ptr(idx), _ptr(packed), N, _stream())
+    if off_ptrs is not None:
+        _lib.call("udp_decode_offset_split", _ptr(out), _ptr(fl), C.c_void_p(off_ptrs[0]),
+                  C.c_void_p(off_ptrs[1]) if fl is not None else None, _ptr(perm), float(kpd), _ptr(c), _ptr(s),
+                  f64, K, w, h, _ptr(preds), _ptr(mv), _ptr(pin), _ptr(idx), _ptr(packed), N, _stream())
+    else:
+        _lib.call("udp_decode_offset", _ptr(out), _ptr(fl), _ptr(perm), float(kpd), _ptr(c), _ptr(s),
+                  f64, K, w, h, _ptr(preds), _ptr(mv), _ptr(pin), _ptr(idx), _ptr(packed), N, _stream())
     r = dict(preds=preds, maxvals=mv, preds_in=pin)
     if want_idx:
         r["idx"] = idx

@@ -60,8 +60,14 @@ from .configs import RSN_SIGMAS as D_RSN  # noqa: E402
 class HostPipeline:
     """Chunked, stream-overlapped codec pass over a HostBatch."""
 
-    def __init__(self, cfg, chunk, n_images, src_hw=(480, 640), device="cuda", n_slots=3):
+    def __init__(self, cfg, chunk, n_images, src_hw=(480, 640), device="cuda", n_slots=3, split_offsets=None):
+        """split_offsets (offset-target configs only; default on): upload only the K classification channels of the
+        two network outputs (one strided 2-D copy per tensor and chunk) and let the decoder gather its 7x7 offset
+        windows straight from the caller's pinned buffers over the host link (udp_decode_offset_split) -- the
+        voting decoder never reads the rest of the offset maps (inference.py:166-167,173-174), so two thirds of
+        the upload of lib/core/function.py:154-169 disappear.  Results are bit-identical."""
         self.cfg, self.chunk, self.dev = cfg, chunk, torch.device(device)
+        self.split = cfg.target_type == "offset" and (split_offsets is None or bool(split_offsets))
         K, C = cfg.num_joints, cfg.channels
         (W, H), (w, h) = cfg.image_size, cfg.heatmap_size
         cs = torch.float64 if cfg.cs_dtype == "float64" else torch.float32
@@ -139,6 +145,7 @@ class HostPipeline:
             self.ptr_host[par] = pinned((n,), torch.int64)
         ptr_host = self.ptr_host[par]
         np.add(self.images.data_ptr(), np.asarray(hb.image_index[:n], np.int64) * self.img_bytes, out=ptr_host.numpy()[:n])
+        off_base = (D.host_device_pointer(hb.out), D.host_device_pointer(hb.out_flipped)) if self.split else None
         with torch.cuda.stream(self.s_up):
             self.s_up.wait_stream(self.s_run)  # kernels of an unsynchronised previous run still read the images
             self.images.copy_(hb.images, non_blocking=True)
@@ -148,10 +155,14 @@ class HostPipeline:
             sel = slice(lo, lo + m)
             with torch.cuda.stream(self.s_up):
                 self.s_up.wait_event(sl["down"])  # slot free again (previous download finished)
-                for key, src in (("center", hb.center), ("scale", hb.scale), ("rot", hb.rot),
-                                 ("joints", hb.joints), ("vis", hb.joints_vis), ("out", hb.out),
-                                 ("fl", hb.out_flipped)):
+                small = (("center", hb.center), ("scale", hb.scale), ("rot", hb.rot), ("joints", hb.joints), ("vis", hb.joints_vis))
+                for key, src in small + (() if self.split else (("out", hb.out), ("fl", hb.out_flipped))):
                     sl[key][:m].copy_(src[sel], non_blocking=True)
+                if self.split:  # classification channels only: rows of h*w floats, every third map
+                    hwb = hb.out.shape[2] * hb.out.shape[3] * 4
+                    for key, src in (("out", hb.out), ("fl", hb.out_flipped)):
+                        D.copy2d_async(sl[key].data_ptr(), 3 * hwb, src.data_ptr() + lo * cfg.channels * hwb, 3 * hwb, hwb,
+                                       m * cfg.num_joints, to_device=True)
                 sl["ptrs"][:m].copy_(ptr_host[sel], non_blocking=True)
                 sl["up"].record()
             with torch.cuda.stream(self.s_run):
@@ -167,8 +178,12 @@ class HostPipeline:
                     tw = sl["vis"][:m, :, 0:1].float()
                 else:
                     _, tw = D.encode_batch(cfg, j3, sl["vis"][:m], out=sl["target"][:m])
+                kw = {}
+                if self.split:  # offset windows: read in place from the caller's pinned buffers
+                    pb = lo * cfg.channels * hb.out.shape[2] * hb.out.shape[3] * 4
+                    kw["off_ptrs"] = (off_base[0] + pb, off_base[1] + pb)
                 r = D.decode_batch(cfg, sl["out"][:m], sl["fl"][:m], sl["center"][:m], sl["scale"][:m],
-                                   want_packed=True)
+                                   want_packed=True, **kw)
                 self.launches += 4 + D.crop_launches(cfg.image_size)
                 sl["ran"].record()
             with torch.cuda.stream(self.s_down):
@@ -184,6 +199,15 @@ class HostPipeline:
         self.ptr_done[par].record(self.s_up)
         if sync:
             self.synchronize()
+
+    def h2d_bytes(self, hb):
+        """Bytes that cross the host link towards the device in one run(hb)."""
+        if not self.split:
+            return hb.h2d_bytes()
+        K, hw4 = self.cfg.num_joints, hb.out.shape[2] * hb.out.shape[3] * 4
+        full = 2 * hb.out.numel() * 4
+        # classification maps by copy; per joint 2 channels x 2 tensors x 7 window rows, two 32-byte sectors each, read in place
+        return hb.h2d_bytes() - full + hb.n * (2 * K * hw4 + K * 2 * 2 * 7 * 64)
 
     def synchronize(self):
         self.s_down.synchronize()
