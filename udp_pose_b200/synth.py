@@ -155,3 +155,48 @@ def nms_persons(images, max_per_image, K, rng, exact=False):
     boxes = np.concatenate([xy.mean(1), s, np.prod(s * 200.0, 1, keepdims=True), rng.uniform(0.05, 1.0, (N, 1))], 1)
     perm = rng.permutation(N)
     return preds[perm], boxes[perm].astype(np.float64), img[perm]
+
+
+def adversarial_offset_maps(cfg, rng):
+    """Adversarial parity set for the offset-voting decoder (inference.py:156-174): float32 [M,3K,h,w].
+    The arg-max is taken on the 15x15-BLURRED classification map, so the rows stress exactly that:
+    0 U(0,1) noise, 1 N(0,1) noise, 2 all-negative, 3 all-zero classification maps (maxval 0: mask false),
+    4 two equal isolated pixels (the blurred map has two bit-identical maxima: first index must win),
+    5 peaks on every border / corner (the 15x15 window and the 7x7 offset windows reflect),
+    6 a single pixel, 7 a plateau of equal values (ties between neighbours after the blur).
+    Offset channels: N(0, 0.3) noise (so a wrong window or a wrong reflection changes the vote)."""
+    w, h = cfg.heatmap_size
+    K = cfg.num_joints
+    cls = []
+    cls.append(rng.uniform(0, 1, (K, h, w)))
+    cls.append(rng.standard_normal((K, h, w)))
+    cls.append(-rng.uniform(0.1, 1, (K, h, w)))
+    cls.append(np.zeros((K, h, w)))
+    t = np.zeros((K, h, w))
+    for k in range(K):
+        y0, x0 = rng.integers(8, h // 2 - 8), rng.integers(8, w - 8)
+        y1, x1 = rng.integers(h // 2 + 8, h - 8), rng.integers(8, w - 8)
+        t[k, y0, x0] = t[k, y1, x1] = 0.75
+    cls.append(t)
+    b = rng.uniform(0, 0.01, (K, h, w))
+    spots = [(0, 0), (0, w - 1), (h - 1, 0), (h - 1, w - 1), (0, w // 2), (h - 1, w // 2), (h // 2, 0), (h // 2, w - 1),
+             (1, 1), (h - 2, w - 2), (3, w - 1), (h - 1, 3)]
+    for k in range(K):
+        y, x = spots[k % len(spots)]
+        b[k, y, x] = 1.0
+    cls.append(b)
+    z = np.zeros((K, h, w))
+    for k in range(K):
+        z[k, rng.integers(0, h), rng.integers(0, w)] = 0.9
+    cls.append(z)
+    p = np.zeros((K, h, w))
+    for k in range(K):
+        y, x = rng.integers(0, h - 12), rng.integers(0, w - 12)
+        p[k, y:y + 4 + k % 8, x:x + 4 + (k * 3) % 8] = 0.5
+    cls.append(p)
+    cls = np.stack(cls)
+    M = cls.shape[0]
+    out = np.zeros((M, K, 3, h, w))
+    out[:, :, 0] = cls
+    out[:, :, 1:] = rng.standard_normal((M, K, 2, h, w)) * 0.3
+    return out.reshape(M, 3 * K, h, w).astype(np.float32)
