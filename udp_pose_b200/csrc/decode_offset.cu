@@ -355,7 +355,7 @@ decode_offset_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
 
 // Third generation (decode_offset_prune.cuh): exact branch-and-bound arg-max.  Persistent CTAs, two-stage TMA
 // feed of (out_i, flipped_i), four barriers per map, the same 32-entry mailbox and batched vote as above.
-template <int W, int H, int NT, int MINB, bool FLIP>
+template <int W, int H, int NT, int MINB, int STAGES, bool FLIP>
 __global__ void __launch_bounds__(NT, MINB)
 decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_fl,
                            DecodeOffsetArgs p, long long maps)
@@ -448,7 +448,10 @@ decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __g
     long long map = blockIdx.x;
     int st = 0, slot = 0;
     if (map < maps && tid == 0) issue_pair(0);
-    for (; map < maps; map += gridDim.x, st ^= 1) {
+    // STAGES == 2: the loads of map i+1 are in flight while map i is decoded (53 KB per CTA).  STAGES == 1: no prefetch,
+    // 27 KB per CTA: twice as many, smaller CTAs per SM hide the load latency and the short serial phases of each other
+    for (; map < maps; map += gridDim.x, st ^= (STAGES == 2 ? 1 : 0)) {
+        const int ns = STAGES == 2 ? (st ^ 1) : 0;  // stage of the next map
         float *P = smem + (2 * st) * G::BUF, *Q = P + G::BUF;
         const long long next = map + gridDim.x;
         nxt.advance();
@@ -495,7 +498,7 @@ decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __g
         const bool anybad = __syncthreads_or(bad);
         // ... and everybody has left the column pass of map i-1, the last reader of the other stage (whose
         // generic-proxy stores were fenced before that map's barrier (4)): prefetch map i+1 into it
-        if (!anybad && next < maps && tid == 0) issue_pair(st ^ 1);
+        if (STAGES == 2 && !anybad && next < maps && tid == 0) issue_pair(ns);
         if (finish && warp == 0) flush_final(NBOX);
         if (anybad) {  // NaN / inf somewhere in the map: the generic, NaN-exact path (clobbers all buffers; no load in flight)
             const int gn = (int)(map / p.K), gk = (int)(map - (long long)gn * p.K);
@@ -503,7 +506,7 @@ decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __g
             decode_offset_generic(p, smem, map, gn, src_of(map), gfl);
             feed.release();
             __syncthreads();
-            if (next < maps && tid == 0) issue_pair(st ^ 1);
+            if (next < maps && tid == 0) issue_pair(ns);
             continue;
         }
 #pragma unroll
@@ -589,6 +592,10 @@ decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __g
         if (lane == 0) { box[B_V + warp] = bv; box[B_I + warp] = __int_as_float(bi); }
         if (tid == 0) box[B_MAP] = __int_as_float((int)map);
         ++slot;
+        if (STAGES == 1) {  // everybody has left the column pass: the only stage may be refilled
+            __syncthreads();
+            if (next < maps && tid == 0) issue_pair(0);
+        }
     }
     __syncthreads();
     if (slot) {
@@ -642,13 +649,14 @@ static int decode_offset_launch(const float *out, const float *out_flipped, cons
         // third generation (exact branch-and-bound arg-max), opt-in with UDP_OFFSET_PRUNE=1: bit-exact (the decode tests
         // pass with it) and a third fewer instructions on peaked maps, but its five short phases per map leave the SM
         // idle more than the three long ones of the full-blur pipe kernel: 2.15 ms against 1.84 ms per 16 384 persons
-#define UDP_OFF_PRUNE(WW, HH, NT, MINB)                                                                  \
+#define UDP_OFF_PRUNE(WW, HH, NT, MINB, STG)                                                                  \
         if (w == WW && h == HH && prune_on) do {                                                 \
             using G = udp::PruneGeom<WW, HH, NT>;                                                \
-            const size_t smem = (G::SMEM > gsmem ? G::SMEM : gsmem) + 128;                       \
+            const size_t need = (size_t)2 * STG * G::BUF * sizeof(float);                        \
+            const size_t smem = (need > gsmem ? need : gsmem) + 128;                             \
             void (*kern)(CUtensorMap, CUtensorMap, udp::DecodeOffsetArgs, long long) =           \
-                out_flipped ? udp::decode_offset_prune_kernel<WW, HH, NT, MINB, true>            \
-                            : udp::decode_offset_prune_kernel<WW, HH, NT, MINB, false>;          \
+                out_flipped ? udp::decode_offset_prune_kernel<WW, HH, NT, MINB, STG, true>       \
+                            : udp::decode_offset_prune_kernel<WW, HH, NT, MINB, STG, false>;     \
             CUtensorMap tm_out, tm_fl;                                                           \
             const bool tma_ok = udp::pipe_make_map(&tm_out, out, WW, HH, G::SR, 3 * maps) &&     \
                                 udp::pipe_make_map(&tm_fl, out_flipped ? out_flipped : out, WW, HH, G::SR, 3 * maps); \
@@ -665,11 +673,12 @@ static int decode_offset_launch(const float *out, const float *out_flipped, cons
         const char *pe = getenv("UDP_OFFSET_PRUNE");
         const bool prune_on = pe && pe[0] == '1';
 #ifndef UDP_PRUNE_NT
-#define UDP_PRUNE_NT 128
-#define UDP_PRUNE_MINB 3
+#define UDP_PRUNE_NT 64
+#define UDP_PRUNE_MINB 6
+#define UDP_PRUNE_STAGES 1
 #endif
-        UDP_OFF_PRUNE(48, 64, UDP_PRUNE_NT, UDP_PRUNE_MINB)
-        UDP_OFF_PRUNE(64, 64, UDP_PRUNE_NT, UDP_PRUNE_MINB)
+        UDP_OFF_PRUNE(48, 64, UDP_PRUNE_NT, UDP_PRUNE_MINB, UDP_PRUNE_STAGES)
+        UDP_OFF_PRUNE(64, 64, UDP_PRUNE_NT, UDP_PRUNE_MINB, UDP_PRUNE_STAGES)
 #undef UDP_OFF_PRUNE
 #ifndef UDP_OFF_NT
 #define UDP_OFF_NT 96
