@@ -296,7 +296,10 @@ __global__ void decode_gaussian_kernel(DecodeGaussArgs p)
 // maps the 32 lanes of one warp finish one mailbox entry each (first build: that tail ran on 7
 // lanes per map while the other warps waited at the next barrier -- 37 % of stall samples were
 // barrier stalls, 19 % of all instructions were the tail).
-template <int W, int H, int NT, int MINB, bool POST, bool FLIP, bool DIV255>
+// NBUF == 3: out_i / T_i, out_{i+1}, flipped.  NBUF == 2 (large maps): no buffer for out_{i+1} -- it is fetched into the
+// only `out` buffer once the column pass has left it; one more CTA per SM (three of 58 KB at 96x72 instead of two of 88 KB)
+// covers the exposed load.
+template <int W, int H, int NT, int MINB, bool POST, bool FLIP, bool DIV255, int NBUF>
 __global__ void __launch_bounds__(NT, MINB)
 decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_fl,
                             DecodeGaussArgs p, long long maps)
@@ -346,18 +349,19 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
         }
     };
 
-    // buffer roles: bP holds out_i (then T_i), bN receives out_{i+1}; buffer 2 always holds the flipped map
+    // buffer roles: bP holds out_i (then T_i), bN receives out_{i+1}; buffer QB always holds the flipped map
+    constexpr int QB = NBUF - 1;
     long long map = blockIdx.x;
-    int bP = 0, bN = 1, slot = 0;
+    int bP = 0, bN = NBUF == 3 ? 1 : 0, slot = 0;
     if (map < maps && threadIdx.x == 0) {
         feed.issue(bP, &tm_out, row_of(map));
-        if (has_fl) feed.issue(2, &tm_fl, fl_row());
+        if (has_fl) feed.issue(QB, &tm_fl, fl_row());
         s_idx[bP] = 0x7fffffff;  // visible to the first atomicMin through barrier (B)
     }
-    for (; map < maps; map += gridDim.x, bP ^= 1, bN ^= 1) {
-        float *bufP = smem + bP * G::BUF, *bufQ = smem + 2 * G::BUF;
+    for (; map < maps; map += gridDim.x, bP ^= (NBUF == 3 ? 1 : 0), bN ^= (NBUF == 3 ? 1 : 0)) {
+        float *bufP = smem + bP * G::BUF, *bufQ = smem + QB * G::BUF;
         feed.wait(bP);  // per-thread wait: no CTA barrier is needed to read a landed map
-        if (has_fl) feed.wait(2);
+        if (has_fl) feed.wait(QB);
         const long long next = map + gridDim.x;
         nxt.advance();
         // mailbox full: one warp finishes the 32 queued maps (one barrier so that the last entry is
@@ -382,23 +386,26 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
         // (B) both raw buffers are consumed and everyone has left the previous column pass:
         // out_{i+1} may land in bN (it held T_{i-1}), T_i may overwrite out_i, flipped_{i+1} may land in Q
         const bool anybad = __syncthreads_or(bad);
-        if (threadIdx.x == 0) {
+        if (NBUF == 3 && threadIdx.x == 0) {
             if (next < maps) feed.issue(bN, &tm_out, row_of(next));
             s_idx[bN] = 0x7fffffff;  // the next map's slot; its last reader passed (B) with us
         }
         if (anybad) {  // a non-finite value: NaN-exact generic path for this map
-            if (next < maps) feed.wait(bN);  // the load in flight must land before the buffers are reused
+            if (NBUF == 3 && next < maps) feed.wait(bN);  // the load in flight must land before the buffers are reused
             __syncthreads();
-            decode_gauss_generic_map<POST>(p, smem, map);  // clobbers all three buffers
+            decode_gauss_generic_map<POST>(p, smem, map);  // clobbers all the buffers
             feed.release();
             __syncthreads();
-            if (next < maps && threadIdx.x == 0) {
-                feed.issue(bN, &tm_out, row_of(next));
-                if (has_fl) feed.issue(2, &tm_fl, fl_row());
+            if (threadIdx.x == 0) {
+                if (NBUF == 2) s_idx[0] = 0x7fffffff;
+                if (next < maps) {
+                    feed.issue(bN, &tm_out, row_of(next));
+                    if (has_fl) feed.issue(QB, &tm_fl, fl_row());
+                }
             }
             continue;
         }
-        if (has_fl && next < maps && threadIdx.x == 0) feed.issue(2, &tm_fl, fl_row());
+        if (has_fl && next < maps && threadIdx.x == 0) feed.issue(QB, &tm_fl, fl_row());
         float M = s_wmax[0];
 #pragma unroll
         for (int q = 1; q < NW; ++q) M = fmaxf(M, s_wmax[q]);
@@ -435,19 +442,27 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
             box[B_MAP] = __int_as_float((int)map);
         }
         ++slot;
+        if (NBUF == 2) {  // (D) everybody has left the column pass: out_{i+1} may land where T_i was
+            feed.release();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                if (next < maps) feed.issue(0, &tm_out, row_of(next));
+                s_idx[0] = 0x7fffffff;
+            }
+        }
     }
     __syncthreads();
     if (slot && warp == 0) flush(slot);
 }
 
-template <int W, int H, int NT, int MINB>
+template <int W, int H, int NT, int MINB, int NBUF>
 static void (*pick_gauss_pipe(bool post, bool flip, bool div))(CUtensorMap, CUtensorMap, DecodeGaussArgs, long long)
 {
-#define UDP_PICK(P, F, D) if (post == P && flip == F && div == D) return decode_gaussian_pipe_kernel<W, H, NT, MINB, P, F, D>;
+#define UDP_PICK(P, F, D) if (post == P && flip == F && div == D) return decode_gaussian_pipe_kernel<W, H, NT, MINB, P, F, D, NBUF>;
     UDP_PICK(true, true, false) UDP_PICK(true, false, false) UDP_PICK(true, true, true) UDP_PICK(true, false, true)
     UDP_PICK(false, true, false) UDP_PICK(false, false, false) UDP_PICK(false, true, true)
 #undef UDP_PICK
-    return decode_gaussian_pipe_kernel<W, H, NT, MINB, false, false, true>;
+    return decode_gaussian_pipe_kernel<W, H, NT, MINB, false, false, true, NBUF>;
 }
 
 }  // namespace udp
@@ -490,12 +505,13 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
     // Streaming fast path: the reference's map shapes, plain or /255 (RSN) pre-scaling, no
     // blurred write-back.  Everything else (and every map holding a NaN/inf) runs the generic code.
     if (!udp_force_generic() && !blurred && (pre_div == 0.0f || pre_div == 255.0f)) {
-#define UDP_GAUSS_PIPE(WW, HH, NT, MINB)                                                             \
+#define UDP_GAUSS_PIPE(WW, HH, NT, MINB, NBUF)                                                          \
         if (w == WW && h == HH) do {                                                             \
             using G = udp::PipeGeom<WW, HH, 3, NT>;                                              \
-            const size_t smem = (G::SMEM > gsmem ? G::SMEM : gsmem) + 128;  /* + alignment slack */ \
+            const size_t need = (size_t)NBUF * G::BUF * sizeof(float);                           \
+            const size_t smem = (need > gsmem ? need : gsmem) + 128;  /* + alignment slack */    \
             void (*kern)(CUtensorMap, CUtensorMap, udp::DecodeGaussArgs, long long) =                   \
-                udp::pick_gauss_pipe<WW, HH, NT, MINB>(post_process != 0, hm_flipped != nullptr, pre_div != 0.0f); \
+                udp::pick_gauss_pipe<WW, HH, NT, MINB, NBUF>(post_process != 0, hm_flipped != nullptr, pre_div != 0.0f); \
             CUtensorMap tm_out, tm_fl;                                                           \
             const bool tma_ok = udp::pipe_make_map(&tm_out, hm, WW, HH, G::SR, maps) &&          \
                                 udp::pipe_make_map(&tm_fl, hm_flipped ? hm_flipped : hm, WW, HH, G::SR, maps); \
@@ -512,9 +528,22 @@ extern "C" int udp_decode_gaussian(const float *hm, const float *hm_flipped,
 #ifndef UDP_GAUSS_MINB
 #define UDP_GAUSS_MINB 4
 #endif
-        UDP_GAUSS_PIPE(48, 64, 96, UDP_GAUSS_MINB)
-        UDP_GAUSS_PIPE(64, 64, 128, 3)
-        UDP_GAUSS_PIPE(72, 96, 288, 2)
+#ifndef UDP_GAUSS_BIG_NBUF
+#define UDP_GAUSS_BIG_NBUF 2
+#define UDP_GAUSS_BIG_MINB 3
+#endif
+#ifndef UDP_GAUSS_NBUF
+#define UDP_GAUSS_NBUF 3
+#endif
+#ifndef UDP_GAUSS_SQ_MINB
+#define UDP_GAUSS_SQ_MINB 3
+#endif
+        UDP_GAUSS_PIPE(48, 64, 96, UDP_GAUSS_MINB, UDP_GAUSS_NBUF)
+        UDP_GAUSS_PIPE(64, 64, 128, UDP_GAUSS_SQ_MINB, UDP_GAUSS_NBUF)
+#ifndef UDP_GAUSS_BIG_NT
+#define UDP_GAUSS_BIG_NT 144   // 144 threads x 3 CTAs x 2 buffers: 2.99 ms per 16 384 persons; 288 x 2 x 3: 3.55; 288 x 3 x 2 (spills): 3.89
+#endif
+        UDP_GAUSS_PIPE(72, 96, UDP_GAUSS_BIG_NT, UDP_GAUSS_BIG_MINB, UDP_GAUSS_BIG_NBUF)
 #undef UDP_GAUSS_PIPE
     }
     auto kern = post_process ? udp::decode_gaussian_kernel<true> : udp::decode_gaussian_kernel<false>;
