@@ -108,3 +108,33 @@ def test_gpu_adv_gaussian(cuda, cid):
 @pytest.mark.parametrize("cid", sorted(CONFIGS))
 def test_gpu_dec8(cuda, cid):
     check_dec8(cuda, cid)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cid", [1, 3, 4, 5])
+def test_gpu_nonfinite_maps_take_the_generic_path_in_every_shape(cuda, orc, cid):
+    """Maps holding NaN / inf are re-done by the shape-generic, NaN-exact code from INSIDE the streaming kernels --
+    whose CTA size differs per shape (96, 144, 128 threads; 144 has a partial last warp, which the generic code's
+    butterfly reductions must cope with).  np.argmax: a NaN wins; masks, maxvals and NaN-ness as the oracle."""
+    from udp_pose_b200 import synth
+    cfg = CONFIGS[cid]
+    w, h = cfg.heatmap_size
+    rng = np.random.default_rng(600 + cid)
+    N, K = 12, cfg.num_joints
+    out, fl = synth.heatmaps(cfg, N, rng)
+    out[1, 2, h // 2, w // 3] = np.nan
+    out[4, 0, 0, 0] = np.inf
+    out[7, K - 1, h - 1, w - 1] = -np.inf
+    fl[9, 3, 5, 5] = np.nan
+    c, s, _ = synth.boxes(cfg, N, rng)
+    with np.errstate(all="ignore"):
+        a = orc.decode(cfg, out, fl, c, s)
+    b = cuda.decode(cfg, out, fl, c, s)
+    assert np.array_equal(a["idx"], b["idx"])
+    assert np.array_equal(np.isnan(a["maxvals"]), np.isnan(b["maxvals"]))
+    ok = ~np.isnan(a["maxvals"])
+    assert np.array_equal(a["maxvals"][ok], b["maxvals"][ok])
+    assert np.array_equal(np.isnan(a["preds"]), np.isnan(b["preds"]))
+    fin = np.isfinite(a["preds"])
+    assert np.array_equal(fin, np.isfinite(b["preds"]))
+    assert np.abs(a["preds"][fin] - b["preds"][fin]).max() <= TOL_PX

@@ -64,10 +64,11 @@ __device__ __forceinline__ bool arg_better(float v1, int i1, float v2, int i2)
 __device__ __forceinline__ void block_argmax(float &v, int &i, float *red_v, int *red_i)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    const unsigned lanes = warp_lanes();
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        const float ov = __shfl_xor_sync(0xffffffffu, v, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        const float ov = shfl_xor_or_self(lanes, v, o);
+        const int oi = shfl_xor_or_self(lanes, i, o);
         if (arg_better(ov, oi, v, i)) { v = ov; i = oi; }
     }
     if (lane == 0) { red_v[warp] = v; red_i[warp] = i; }

@@ -122,6 +122,20 @@ __device__ __forceinline__ f32x2 ffma2pp(f32x2 a, f32x2 b, f32x2 c)
     return d;
 }
 
+// Butterfly reductions in blocks whose size need not be a multiple of 32 (the last warp is then partial): shuffles
+// name the lanes that exist, and a partner that does not exist contributes the lane's own value.
+__device__ __forceinline__ unsigned warp_lanes()
+{
+    const unsigned n = blockDim.x - (threadIdx.x & ~31u);
+    return n >= 32u ? 0xffffffffu : ((1u << n) - 1u);
+}
+template <class T>
+__device__ __forceinline__ T shfl_xor_or_self(unsigned lanes, T v, int o)
+{
+    const T u = __shfl_xor_sync(lanes, v, o);
+    return ((lanes >> ((threadIdx.x & 31u) ^ (unsigned)o)) & 1u) ? u : v;
+}
+
 // Wait until the mbarrier at shared address `mbar` completes the phase of parity `parity`
 // (try_wait suspends the thread in hardware between polls).
 __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity)

@@ -241,6 +241,9 @@ __device__ __forceinline__ uint32_t crop_tile_pixel(int X, int Y, int pitch, int
 #ifndef UDP_CROP_AXIS
 #define UDP_CROP_AXIS 1
 #endif
+#ifndef UDP_CROP_F32_FEWER
+#define UDP_CROP_F32_FEWER 1
+#endif
 #ifndef UDP_CROP_LARGE_MINB
 #define UDP_CROP_LARGE_MINB 6
 #endif
@@ -672,16 +675,33 @@ __device__ unsigned int g_tmap_busy[TM_SLOTS];
 template <int ROWS, int WC, class OUT>
 __device__ __forceinline__ void crop_gather_rows(const int2 *rq, int adx, int bdx, int pitch, int K0, OUT &out)
 {
-    int2 q[ROWS];
+    // The float32 policy's emit is ~100 instructions: unrolled into every row of every tile shape it overflowed the
+    // instruction cache (`no_instruction` stalls at 5.8 per issue, 3.0 -> 6.0 ms): its row loops stay rolled.
+    if constexpr (OUT::IS_F32) {
+        int2 q0 = rq[0];
+        CropTaps cur = crop_tile_load(q0.x + adx, q0.y + bdx, pitch, K0);
+#pragma unroll 1
+        for (int i = 0; i < ROWS; ++i) {
+            CropTaps nxt = cur;
+            if (i + 1 < ROWS) {
+                const int2 q = rq[4 * (i + 1)];
+                nxt = crop_tile_load(q.x + adx, q.y + bdx, pitch, K0);
+            }
+            out.template emit_at<CT_THREADS / 32, WC>(crop_tile_finish(cur), i);
+            cur = nxt;
+        }
+    } else {
+        int2 q[ROWS];
 #pragma unroll
-    for (int i = 0; i < ROWS; ++i) q[i] = rq[4 * i];
-    CropTaps cur = crop_tile_load(q[0].x + adx, q[0].y + bdx, pitch, K0);
+        for (int i = 0; i < ROWS; ++i) q[i] = rq[4 * i];
+        CropTaps cur = crop_tile_load(q[0].x + adx, q[0].y + bdx, pitch, K0);
 #pragma unroll
-    for (int i = 0; i < ROWS; ++i) {
-        CropTaps nxt;
-        if (i + 1 < ROWS) nxt = crop_tile_load(q[i + 1].x + adx, q[i + 1].y + bdx, pitch, K0);
-        out.template emit_at<CT_THREADS / 32, WC>(crop_tile_finish(cur), i);
-        if (i + 1 < ROWS) cur = nxt;
+        for (int i = 0; i < ROWS; ++i) {
+            CropTaps nxt;
+            if (i + 1 < ROWS) nxt = crop_tile_load(q[i + 1].x + adx, q[i + 1].y + bdx, pitch, K0);
+            out.template emit_at<CT_THREADS / 32, WC>(crop_tile_finish(cur), i);
+            if (i + 1 < ROWS) cur = nxt;
+        }
     }
 }
 
@@ -722,7 +742,8 @@ __device__ __forceinline__ void crop_gather_axis(const int2 *rq, unsigned base, 
     int2 qn = rq[0];
     int cur = qn.x - pitch;  // offset of the source row held in hb
     CropHRow ht = {0u, 0u, 0u}, hb = {0u, 0u, 0u};
-#pragma unroll
+    constexpr int UNR = OUT::IS_F32 ? 1 : RW;
+#pragma unroll UNR
     for (int i = 0; i < RW; ++i) {
         const int2 qc = qn;
         if (i + 1 < RW) qn = rq[i + 1];  // one row ahead (all of them at once cost registers: spills in this loop)
@@ -775,7 +796,7 @@ __device__ __forceinline__ int crop_pick_pitch(const CropPlan &pl, const float *
 }
 
 template <class OUT, int CT_SMEM, int WC>
-__global__ void __launch_bounds__(CT_THREADS, ((CT_SMEM > 30 * 1024) ? 6 : UDP_CROP_LARGE_MINB) - (OUT::IS_F32 ? 1 : 0))  // CTAs per SM: footprint buffers, registers
+__global__ void __launch_bounds__(CT_THREADS, ((CT_SMEM > 30 * 1024) ? 6 : UDP_CROP_LARGE_MINB) - (OUT::IS_F32 ? UDP_CROP_F32_FEWER : 0))  // CTAs per SM: footprint buffers, registers
 warp_affine_u8_tma_kernel(const __grid_constant__ CUtensorMap tmpl, const uint8_t *const *src_ptrs,
                           const int32_t *src_h, const int32_t *src_w, const int32_t *src_stride,
                           const float *M, typename OUT::Args oargs, int W_, int H)

@@ -241,11 +241,12 @@ __device__ __noinline__ void decode_gauss_generic_map(const DecodeGaussArgs &p, 
             if (keep) *reinterpret_cast<float4 *>(B + y * w + x) = s;
         });
         // block min / max (np.min / np.max propagate NaN)
+        const unsigned lanes = warp_lanes();
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
-            mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-            has_nan |= __shfl_xor_sync(0xffffffffu, has_nan, o);
+            mn = fminf(mn, shfl_xor_or_self(lanes, mn, o));
+            mx = fmaxf(mx, shfl_xor_or_self(lanes, mx, o));
+            has_nan |= shfl_xor_or_self(lanes, has_nan, o);
         }
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
         if (lane == 0) { red_mn[warp] = mn; red_mx[warp] = mx; red_nan[warp] = has_nan; }
@@ -321,6 +322,13 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int pr = threadIdx.x % G::HP, xs = threadIdx.x / G::HP;
     constexpr bool has_fl = FLIP;
+    // NT need not be a multiple of 32 (144 at 96x72): the last warp is then partial.  Shuffles name the lanes that
+    // exist, and a butterfly partner that does not exist contributes the lane's own value.
+    const unsigned wmask = (NT % 32 != 0 && warp == NW - 1) ? ((1u << (NT % 32)) - 1u) : 0xffffffffu;
+    auto xor_or_self = [&](float v, int o) {
+        const float u = __shfl_xor_sync(wmask, v, o);
+        return (NT % 32 == 0 || ((wmask >> (lane ^ o)) & 1u)) ? u : v;
+    };
 
     PipeFeed<W, H, R, NT> feed;
     feed.init(smem, s_bars);
@@ -379,7 +387,7 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
         const float lm = pipe_local_max<W, H, R, NT>(v, fs);
         float wm = lm;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+        for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, xor_or_self(wm, o));
         if (lane == 0) s_wmax[warp] = wm;
         const bool bad = !(fabsf(fs) < INFINITY);
         feed.release();  // this thread's T_{i-1} stores (in bN) are ordered before the bulk load below
@@ -431,8 +439,8 @@ decode_gaussian_pipe_kernel(const __grid_constant__ CUtensorMap tm_out, const __
             });
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
-                mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                mn = fminf(mn, xor_or_self(mn, o));
+                mx = fmaxf(mx, xor_or_self(mx, o));
             }
             if (lane == 0) { box[B_MN + warp] = mn; box[B_MX + warp] = mx; }
         }
