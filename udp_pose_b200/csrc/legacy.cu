@@ -192,6 +192,180 @@ rsn_get_results_kernel(const __grid_constant__ LegacyArgs p)
     p.maxvals[m] = (double)score;
 }
 
+// ---------------------------------------------------------------------------------------
+// Second generation (kernel sizes known at compile time: 5, 9, 11).  Same arithmetic, operation by operation, as the
+// kernel above; what changes is how often a value is touched.  ncu on the first kernel (profiles/r01_rsn_legacy_v2_ncu.txt):
+// 24 000 warp-instructions per 64x48 map of which a tenth are the float64 blur -- five shared loads and five
+// float -> double conversions per row-pass output, five loads per column-pass output, 68-element rows walked in
+// 32-lane steps, a branchy double-precision top-2 merged through shuffles.  Here
+//   * row pass: a thread owns (row, 17-column segment) and slides along it with the converted window in registers:
+//     one load and one conversion per input value; out-of-map taps are zeros in registers (no zero frame in memory);
+//   * column pass: a thread owns (column, 24-row segment) of the rows that can see the map, window in registers:
+//     one load per input value; rows that only see the zero frame are exactly +0 and are represented by the two
+//     lowest indices of the padded map, (0.0, 0) and (0.0, 1) -- all the arg-max rule can ever pick from them;
+//   * top-2: per thread as before (one well-predicted branch per element), across threads as two plain (value,
+//     index) arg-max reductions: the global best, then the best of "my second if I own the best, else my first".
+// ---------------------------------------------------------------------------------------
+constexpr int LG_SEGX = 17, LG_SEGY = 24;
+
+__device__ __forceinline__ void lg_block_argmax(double &v, int &i, double *red_v, int *red_i)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        if (lg_before(ov, oi, v, i)) { v = ov; i = oi; }
+    }
+    if (lane == 0) { red_v[warp] = v; red_i[warp] = i; }
+    __syncthreads();
+    v = red_v[0]; i = red_i[0];
+#pragma unroll
+    for (int q = 1; q < LG_THREADS / 32; ++q)
+        if (lg_before(red_v[q], red_i[q], v, i)) { v = red_v[q]; i = red_i[q]; }
+    __syncthreads();  // the scratch is reused
+}
+
+// three CTAs per SM for the 5-tap kernel (80 registers; 4.39 ms against 5.25 at two); the 9- and 11-tap windows spill there
+template <int NK>
+__global__ void __launch_bounds__(LG_THREADS, NK <= 5 ? 3 : 2)
+rsn_get_results_fast_kernel(const __grid_constant__ LegacyArgs p)
+{
+    extern __shared__ __align__(16) unsigned char lg_smem[];
+    __shared__ double s_rv[LG_THREADS / 32];
+    __shared__ int s_ri[LG_THREADS / 32];
+    constexpr int n = NK, r = NK >> 1, B = LG_BORDER;
+    const int w = p.w, h = p.h;
+    const int PW = w + 2 * B;
+    double *T0 = reinterpret_cast<double *>(lg_smem);            // [2r + h + 2r][PW] row-pass result inside 2r zero rows
+    double *T = T0 + 2 * r * PW;                                 // row 0 of the map
+    float *S = reinterpret_cast<float *>(T0 + (size_t)(h + 4 * r) * PW);  // [h][w] the (flip-averaged) map
+    const long long m = blockIdx.x;
+    const int person = (int)(m / p.K), joint = (int)(m - (long long)person * p.K);
+    const float *src = p.out + m * (long long)(h * w);
+    const float *fl = p.out_flipped ? p.out_flipped + ((long long)person * p.K + p.flip_perm[joint]) * (long long)(h * w) : nullptr;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 2 * r * PW; i += LG_THREADS) { T0[i] = 0.0; T[h * PW + i] = 0.0; }
+    // ---- stage the map (flip_back + average, test.py:92-96)
+    if ((w & 3) == 0 && (((uintptr_t)src | (uintptr_t)fl) & 15) == 0) {
+        const int w4 = w >> 2, nv = h * w4;
+        int y = tid / w4, x4 = tid - y * w4;                     // one division per thread, then incremental
+        const int dy = LG_THREADS / w4, dx = LG_THREADS - dy * w4;
+        for (int j0 = tid; j0 < nv; j0 += 4 * LG_THREADS) {
+            float4 a[4], f[4];
+            int yy[4], xx[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                yy[u] = y; xx[u] = x4 << 2;
+                if (j0 + u * LG_THREADS < nv) {
+                    a[u] = __ldcs(reinterpret_cast<const float4 *>(src + y * w + xx[u]));
+                    if (fl) f[u] = __ldcs(reinterpret_cast<const float4 *>(fl + y * w + (w - 4 - xx[u])));
+                }
+                y += dy; x4 += dx;
+                if (x4 >= w4) { x4 -= w4; ++y; }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (j0 + u * LG_THREADS < nv) {
+                    float4 v = a[u];
+                    if (fl) {
+                        v.x = __fmul_rn(__fadd_rn(v.x, f[u].w), 0.5f); v.y = __fmul_rn(__fadd_rn(v.y, f[u].z), 0.5f);
+                        v.z = __fmul_rn(__fadd_rn(v.z, f[u].y), 0.5f); v.w = __fmul_rn(__fadd_rn(v.w, f[u].x), 0.5f);
+                    }
+                    *reinterpret_cast<float4 *>(S + yy[u] * w + xx[u]) = v;
+                }
+            }
+        }
+    } else {
+        for (int y = tid >> 5; y < h; y += LG_THREADS / 32)
+            for (int x = tid & 31; x < w; x += 32) {
+                float v = src[y * w + x];
+                if (fl) v = __fmul_rn(__fadd_rn(v, fl[y * w + (w - 1 - x)]), 0.5f);
+                S[y * w + x] = v;
+            }
+    }
+    __syncthreads();
+    // ---- row pass: fused chain, left to right; thread = (row y, columns xp0 .. xp0 + 16 of the padded row)
+    {
+        const int nsx = (PW + LG_SEGX - 1) / LG_SEGX, items = h * nsx;
+        for (int it = tid; it < items; it += LG_THREADS) {
+            const int y = it / nsx, xp0 = (it - y * nsx) * LG_SEGX;
+            const float *srow = S + y * w;
+            double d[LG_SEGX + n - 1];                            // d[j] = padded-row element xp0 + j - r  <->  map column xp0 + j - r - B
+#pragma unroll
+            for (int j = 0; j < LG_SEGX + n - 1; ++j) {
+                const int x = xp0 + j - r - B;
+                d[j] = (x >= 0 && x < w) ? (double)srow[x] : 0.0;
+            }
+            double *trow = T + y * PW + xp0;
+#pragma unroll
+            for (int o = 0; o < LG_SEGX; ++o) {
+                double acc = __dmul_rn(p.k[0], d[o]);
+#pragma unroll
+                for (int t = 1; t < n; ++t) acc = fma(p.k[t], d[o + t], acc);
+                if (xp0 + o < PW) trow[o] = acc;
+            }
+        }
+    }
+    __syncthreads();
+    // ---- column pass over the rows that can see the map (yp = B - r .. B + h + r - 1); thread = (column, 24 rows)
+    Top2 best;
+    best.init();
+    if (tid == 0) { best.push(0.0, 0); best.push(0.0, 1); }       // the all-zero rows above (B > r: indices 0 and 1 are theirs)
+    {
+        const int AR = h + 2 * r, nsy = (AR + LG_SEGY - 1) / LG_SEGY, items = PW * nsy;
+        for (int it = tid; it < items; it += LG_THREADS) {
+            const int sy = it / PW, xp = it - sy * PW;
+            const int y0 = sy * LG_SEGY - r;                      // map row of the first output of this segment
+            const double *col = T + xp;                          // T row y lives at col[y * PW]; rows -2r .. h + 2r - 1 exist
+            double c[LG_SEGY + 2 * r];
+#pragma unroll
+            for (int j = 0; j < LG_SEGY + 2 * r; ++j) {
+                const int y = y0 - r + j;
+                c[j] = (y < h + 2 * r) ? col[y * PW] : 0.0;       // (y >= -2r always; past the zero rows below only in a partial segment)
+            }
+#pragma unroll
+            for (int o = 0; o < LG_SEGY; ++o) {
+                double acc = __dmul_rn(p.k[r], c[o + r]);
+#pragma unroll
+                for (int t = 1; t <= r; ++t) acc = __dadd_rn(acc, __dmul_rn(p.k[r + t], __dadd_rn(c[o + r + t], c[o + r - t])));
+                const int y = y0 + o;
+                if (y < h + r && acc > best.v2) best.push(acc, (y + B) * PW + xp);
+            }
+        }
+    }
+    // ---- top-2 across the block
+    double v1 = best.v1;
+    int i1 = best.i1;
+    lg_block_argmax(v1, i1, s_rv, s_ri);
+    double v2 = best.i1 == i1 ? best.v2 : best.v1;
+    int i2 = best.i1 == i1 ? best.i2 : best.i1;
+    lg_block_argmax(v2, i2, s_rv, s_ri);
+    if (tid != 0) return;
+    // first arg-max, then arg-max of the map with that element set to 0 (test.py:44-50)
+    if (lg_before(0.0, i1, v2, i2)) i2 = i1;
+    const int yi = i1 / PW - B, xi = i1 % PW - B;
+    const int px = (i2 % PW) - (i1 % PW), py = (i2 / PW) - (i1 / PW);
+    double x = (double)xi, y = (double)yi;
+    const double ln = __dsqrt_rn((double)(px * px + py * py));  // int ** 0.5: numpy's sqrt fast path
+    if (ln > 1e-3) {
+        x = __dadd_rn(x, __ddiv_rn(__dmul_rn(p.shift, (double)px), ln));
+        y = __dadd_rn(y, __ddiv_rn(__dmul_rn(p.shift, (double)py), ln));
+    }
+    x = fmax(0.0, fmin(x, (double)(w - 1)));
+    y = fmax(0.0, fmin(y, (double)(h - 1)));
+    const int rx = (int)rint(x), ry = (int)rint(y);               // round(): half to even
+    const float raw = S[ry * w + rx];
+    const float score = __fadd_rn(__fdiv_rn(raw, 255.0f), 0.5f);   // score_map = out / 255 + 0.5 (float32)
+    const float s0 = __fmul_rn(p.scale[2 * person], 200.0f), s1 = __fmul_rn(p.scale[2 * person + 1], 200.0f);  // scales *= 200 (float32)
+    const double kx = __dadd_rn(__dmul_rn(x, 4.0), 2.0), ky = __dadd_rn(__dmul_rn(y, 4.0), 2.0);
+    p.preds[2 * m] = __dsub_rn(__dadd_rn(__dmul_rn(__ddiv_rn(kx, (double)p.in_w), (double)s0), (double)p.center[2 * person]),
+                               (double)__fmul_rn(s0, 0.5f));
+    p.preds[2 * m + 1] = __dsub_rn(__dadd_rn(__dmul_rn(__ddiv_rn(ky, (double)p.in_h), (double)s1), (double)p.center[2 * person + 1]),
+                                   (double)__fmul_rn(s1, 0.5f));
+    p.maxvals[m] = (double)score;
+}
+
 }  // namespace udp
 
 extern "C" int udp_rsn_get_results(const float *outputs, const float *outputs_flipped, const int32_t *flip_perm,
@@ -212,11 +386,16 @@ extern "C" int udp_rsn_get_results(const float *outputs, const float *outputs_fl
     a.shift = shift;
     a.K = K; a.w = w; a.h = h; a.in_w = in_w; a.in_h = in_h; a.n = kernel;
     const int PW = w + 2 * udp::LG_BORDER, SW = PW + 2 * (kernel >> 1);
-    const size_t smem = (size_t)(h + 4 * (kernel >> 1)) * PW * sizeof(double) + (size_t)h * SW * sizeof(float);
+    const char *le = getenv("UDP_LEGACY_FIRST_GEN");  // UDP_LEGACY_FIRST_GEN=1: the first-generation kernel for every size (tests)
+    const bool first_gen = (le && le[0] == '1') || !(kernel == 5 || kernel == 9 || kernel == 11);
+    // the second-generation kernel keeps the map without its zero frame
+    const size_t smem = (size_t)(h + 4 * (kernel >> 1)) * PW * sizeof(double) + (size_t)h * (first_gen ? SW : w) * sizeof(float);
     if (smem > 200 * 1024) return UDP_EINVAL;
-    void (*kern)(udp::LegacyArgs) = kernel == 5 ? udp::rsn_get_results_kernel<5>
-                                  : kernel == 9 ? udp::rsn_get_results_kernel<9>
-                                  : kernel == 11 ? udp::rsn_get_results_kernel<11> : udp::rsn_get_results_kernel<0>;
+    void (*kern)(udp::LegacyArgs) = first_gen ? (kernel == 5 ? udp::rsn_get_results_kernel<5> : kernel == 9 ? udp::rsn_get_results_kernel<9>
+                                                : kernel == 11 ? udp::rsn_get_results_kernel<11> : udp::rsn_get_results_kernel<0>)
+                                  : kernel == 5 ? udp::rsn_get_results_fast_kernel<5>
+                                  : kernel == 9 ? udp::rsn_get_results_fast_kernel<9>
+                                  : kernel == 11 ? udp::rsn_get_results_fast_kernel<11> : udp::rsn_get_results_kernel<0>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     kern<<<(unsigned)maps, udp::LG_THREADS, smem, (cudaStream_t)stream>>>(a);
