@@ -44,7 +44,8 @@ def build(force=False, verbose=False):
         log.append("== %s ==\n%s" % (s, out))
         if p.returncode != 0:
             raise RuntimeError("nvcc failed on %s:\n%s" % (s, out))
-    subprocess.check_call([NVCC, "-shared", "-o", OUT] + objs + ["-lcudart"])
+    # the same -gencode at link time: nvcc's default device-link target would add an empty sm_52 image to the library
+    subprocess.check_call([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + objs + ["-lcudart"])
     with open(os.path.join(CSRC, "ptxas.log"), "w") as f:
         f.write("\n".join(log))
     if verbose:
