@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--no-fused", action="store_true", help="skip the 8(f)-1 fused crop+normalize timing")
     ap.add_argument("--no-configs", action="store_true", help="skip the `configs` block (the other BASELINE.json configs)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the `sweep` block (cfg-5 strong-scaling sweep, 1 Ki .. 1 Mi persons)")
+    ap.add_argument("--no-sweep-graphs", action="store_true", help="sweep: direct launches instead of CUDA-graph replay of each chunk pass")
     ap.add_argument("--config", type=int, default=CFG_ID)
     ap.add_argument("--images", type=int, default=N_IMAGES, help="source image pool (SURVEY 8d: 64; 256 exceeds L2)")
     return ap.parse_args()
@@ -576,7 +577,7 @@ SWEEP_POINTS = [1 << 10, 1 << 12, 1 << 14, 1 << 16, 1 << 18, 1 << 20]
 SWEEP_CHUNK = 1 << 14
 
 
-def run_sweep(sb, local):
+def run_sweep(sb, local, use_graphs=True):
     """BASELINE.json configs[4]: the large-batch sweep, STRONG scaling -- a point is N persons in total, rank r
     owns the contiguous block of ceil(N/R) (RSN/lib/utils/dataloader.py:88-93), processed as a stream of chunks
     of at most 16 Ki persons from the resident pool of `sb` (1 Mi persons of network output would be 418 GB; a
@@ -584,17 +585,24 @@ def run_sweep(sb, local):
     warm-up pass, then `reps` timed passes (CUDA events, max over ranks per pass), the MEDIAN reported, clocks
     sampled over the timed passes."""
     torch, dist, D, wl, cfg, world, rank = sb.torch, sb.dist, sb.D, sb.wl, sb.cfg, sb.world, sb.rank
-    srcs = {}
+    srcs, graph_note = {}, []
 
-    def chunk_pass(m):
+    graphs = {}
+
+    def chunk_kernels(m):
         sl = slice(0, m)
         M = D.warp_matrices(wl["center"][sl], wl["scale"][sl], wl["rot"][sl], cfg.image_size)
         D.crop_batch(srcs[m], M, cfg.image_size, out=sb.crop[sl])
         D.rotate_points_batch(wl["joints"][sl], wl["rot"][sl], wl["center"][sl], wl["scale"][sl], cfg.image_size, out=sb.j3[sl])
         D.encode_batch(cfg, sb.j3[sl], wl["vis"][sl], out=sb.target[sl])
-        r = D.decode_batch(cfg, wl["out"][sl], wl["flipped"][sl], wl["center"][sl], wl["scale"][sl], want_packed=True)
+        return D.decode_batch(cfg, wl["out"][sl], wl["flipped"][sl], wl["center"][sl], wl["scale"][sl], want_packed=True)["packed"]
+
+    def chunk_pass(m):
+        # the five launches of a chunk replay from a CUDA graph (udp_pose_b200.graphs.CapturedPass: below a few thousand
+        # persons a pass is launch-bound); the one collective stays outside the capture
+        packed = graphs[m].replay() if m in graphs else chunk_kernels(m)
         if world > 1:
-            dist.all_gather_into_tensor(sb.gathered[: world * m], r["packed"])
+            dist.all_gather_into_tensor(sb.gathered[: world * m], packed)
 
     points = []
     for N in SWEEP_POINTS:
@@ -603,6 +611,12 @@ def run_sweep(sb, local):
         for m in set(chunks):                                  # per-person image tables: host work, outside the timing
             if m not in srcs:
                 srcs[m] = D.SourceImages(wl["images"], wl["image_index"][:m])
+                if use_graphs:
+                    try:
+                        from udp_pose_b200.graphs import CapturedPass
+                        graphs[m] = CapturedPass(lambda m=m: chunk_kernels(m))
+                    except Exception as exc:  # capture unavailable: direct launches (recorded in the block)
+                        graph_note.append(str(exc)[:80])
         reps = 7 if per <= (1 << 16) else 3
         ts = []
         sampler = ClockSampler(local)
@@ -635,6 +649,7 @@ def run_sweep(sb, local):
                        "persons_per_s": round(N / (ms * 1e-3)), "clocks": clocks})
     return {"cfg": cfg_id_of(cfg), "workload": cfg.name, "scaling": "strong", "n_gpus": world,
             "timing": "CUDA events, max over ranks per pass, median of `reps` passes after one warm-up pass",
+            "cuda_graphs": bool(graphs), "cuda_graph_errors": graph_note,
             "points": points}
 
 
@@ -860,12 +875,12 @@ def run_ours(args):
                               "encode_path_frac": p2["encode_path"]["frac"], "decode_path_frac": p2["decode_path"]["frac"],
                               "gather_ms": round(m["stage_ms"]["gather"], 4), "clocks": m["clocks"]})
             if cid == SWEEP_CFG and not args.no_sweep and B >= SWEEP_CHUNK:  # the sweep draws its chunks from this pool
-                sweep = run_sweep(o, local)
+                sweep = run_sweep(o, local, not args.no_sweep_graphs)
             o.free()
             del o
     if sweep is None and not args.no_sweep:
         o = StepBench(CONFIGS[SWEEP_CFG], SWEEP_CHUNK, rank, world, torch, dist, D)
-        sweep = run_sweep(o, local)
+        sweep = run_sweep(o, local, not args.no_sweep_graphs)
         o.free()
         del o
 
