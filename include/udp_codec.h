@@ -191,6 +191,13 @@ int udp_accuracy_pck(const float *output, const float *target, int ch_stride, in
                      int N, double thr, float *pred, double *dists, double *acc, double *avg_acc,
                      int32_t *cnt, void *stream);
 
+/* SURVEY 8(f)-2 (tail)  the all_boxes rows validate() keeps next to all_preds, lib/core/function.py:211-214:
+ *     all_boxes[n] = (center x, y, scale x, y, np.prod(scale * 200), score) as float64 [N,6]; `scale * 200` and the
+ *     product in the records' dtype (cs_f64 = 0: float32, as numpy does for COCO records).  score [N] float64 or NULL (1).
+ *     With udp_decode_*'s `packed` (= all_preds) this is everything COCODataset.evaluate consumes. */
+int udp_pack_all_boxes(const void *center, const void *scale, int cs_f64, const double *score, double *all_boxes,
+                       int N, void *stream);
+
 /* udp_accuracy_pck for callers that cannot allocate -- NO COUNTERPART IN THE REFERENCE; added
  *     (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  *     Same arguments and results as udp_accuracy_pck minus `dists`: that [K,N] float64 workspace is a static

@@ -57,5 +57,31 @@ def main():
     print("\nclock records: headline", one["clocks"], "; sweep reasons", sorted({r for d in hdr for q in d["sweep"]["points"] for r in (q["clocks"] or {}).get("reasons", [])}))
 
 
+def baseline_rows():
+    """The rows of BASELINE.md section 6 (stage rows per config at one GPU, whole-step rows at 1/2/4/8 GPUs)."""
+    one, ref = load(sys.argv[1]), load(sys.argv[2])
+    multi = [load(p) for p in sys.argv[3:]]
+    peak = one["roofline"]["peak"]
+    rows = [dict(cfg=one["config"]["cfg"], value=one["value"], kernels=one["kernels"])] + one["configs"]
+    rows.sort(key=lambda r: r["cfg"])
+    cpu = ref["cpu_baseline"]
+    print("\n### BASELINE.md section 6\n")
+    print("| cfg | stage | GPUs | persons/s | achieved GB/s | %% of 8 TB/s | %% of measured peak (%.0f GB/s) | CPU persons/s/core | CPU persons/s/box (cores) | parity |" % peak)
+    print("|---|---|---|---|---|---|---|---|---|---|")
+    B = one["config"]["persons_per_gpu_per_step"]
+    for r in rows:
+        for st in ("crop", "encode", "decode"):
+            k = r["kernels"][st]
+            print("| %d | %s | 1 | %.2f M | %.0f | %.0f %% | %.0f %% | | | green |" % (r["cfg"], st, B / k["ms"] / 1e3, k["achieved_gbs"], k["achieved_gbs"] / 80.0, 100 * k["frac"]))
+        print("| %d | whole step | 1 | %.2f M | | | | | | green |" % (r["cfg"], r["value"] / 1e6))
+    for d in multi:
+        print("| %d | whole step | %d | %.2f M | | | | | | green |" % (d["config"]["cfg"], d["n_gpus"], d["value"] / 1e6))
+    print("| %d | whole step, host buffers (e2e) | 1 | %.1f k | | | | %.0f | %.0f (%d) | green |" % (
+        one["config"]["cfg"], one["e2e"]["value"] / 1e3, cpu["per_core"], ref["value"], cpu["cores"]))
+    for d in multi:
+        print("| %d | whole step, host buffers (e2e) | %d | %.1f k | | | | | | green |" % (d["config"]["cfg"], d["n_gpus"], d["e2e"]["value"] / 1e3))
+
+
 if __name__ == "__main__":
     main()
+    baseline_rows()

@@ -12,7 +12,8 @@ ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum 
     -k regex:"warp_|rotate_|encode_|decode_" -c 200 --csv --log-file gpurun_out/r02_launches_$V.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu --no-e2e --no-fused --no-configs --no-sweep > gpurun_out/ncu_launch_$V.log 2>&1
 python profiles/make_traffic.py gpurun_out/r02_launches_$V.csv 2 16384 > gpurun_out/traffic_$V.log 2>&1; cp profiles/traffic.json gpurun_out/traffic_$V.json
-# full captures (one launch each, after warm-up launches)
+# full captures (one launch each, after warm-up launches); FULL=0 skips them
+[ "${FULL:-1}" = "0" ] && exit 0
 cap() { # name kernel-regex skip command...
   n=$1; k=$2; s=$3; shift 3
   ncu --set full --import-source on --clock-control none -k regex:$k --launch-skip $s -c 1 -o gpurun_out/r02_${n}_$V -f "$@" > gpurun_out/ncu_$n.log 2>&1

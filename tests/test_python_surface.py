@@ -234,3 +234,21 @@ def test_accuracy_ignores_thr_like_the_reference(R):
     for thr in (0.5, 0.1, 0.9):
         acc, avg, cnt, pred = R.accuracy(out, tgt, thr=thr)
         assert np.array_equal(acc, gold["cfg1_acc"]) and float(avg) == float(gold["cfg1_avg"]) and cnt == int(gold["cfg1_cnt"])
+
+
+@pytest.mark.parametrize("cid", [1, 4])
+def test_pack_all_boxes_equals_the_reference_lines(R, cid):
+    """lib/core/function.py:211-214, executed literally in numpy on float32 (COCO) and float64 (MPII) records."""
+    from udp_pose_b200 import device_api as D, synth
+    cfg = CONFIGS[cid]
+    rng = np.random.default_rng(40 + cid)
+    c, s, _ = synth.boxes(cfg, 257, rng)
+    score = rng.uniform(0, 1, 257)
+    all_boxes = np.zeros((257, 6))
+    all_boxes[:, 0:2] = c[:, 0:2]
+    all_boxes[:, 2:4] = s[:, 0:2]
+    all_boxes[:, 4] = np.prod(s * 200, 1)
+    all_boxes[:, 5] = score
+    got = D.pack_all_boxes(c, s, score).cpu().numpy()
+    assert got.dtype == np.float64 and same_bits(got, all_boxes)
+    assert same_bits(D.pack_all_boxes(c, s).cpu().numpy()[:, :5], all_boxes[:, :5])

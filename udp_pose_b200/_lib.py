@@ -20,6 +20,7 @@ SIGNATURES = {
     "udp_warp_affine_launches": [_i, _i],
     "udp_accuracy_pck": [_vp, _vp, _i, _i, _i, _i, _i, C.c_double, _vp, _vp, _vp, _vp, _vp, _vp],
     "udp_accuracy_pck_noalloc": [_vp, _vp, _i, _i, _i, _i, _i, C.c_double, _vp, _vp, _vp, _vp, _vp],
+    "udp_pack_all_boxes": [_vp, _vp, _i, _vp, _vp, _i, _vp],
     "udp_decode_quarter": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "udp_rsn_get_results": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _d, _vp, _vp, _i, _vp],
     "udp_aid_erase": [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _i, _vp],

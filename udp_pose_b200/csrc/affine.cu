@@ -239,6 +239,39 @@ extern "C" int udp_fliplr_joints(const double *joints, const double *joints_vis,
     return 0;
 }
 
+// all_boxes rows of validate() (lib/core/function.py:211-214): (cx, cy, sx, sy, prod(s * 200), score) in float64.
+// s * 200 and the product run in the records' dtype (float32 for COCO: numpy keeps float32 through `s*200` and np.prod).
+namespace udp {
+__global__ void pack_all_boxes_kernel(const void *center, const void *scale, int cs_f64, const double *score, double *out, int N)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    double c0, c1, s0, s1, area;
+    if (cs_f64) {
+        const double *c = reinterpret_cast<const double *>(center) + 2 * (size_t)n, *s = reinterpret_cast<const double *>(scale) + 2 * (size_t)n;
+        c0 = c[0]; c1 = c[1]; s0 = s[0]; s1 = s[1];
+        area = __dmul_rn(__dmul_rn(s0, 200.0), __dmul_rn(s1, 200.0));
+    } else {
+        const float *c = reinterpret_cast<const float *>(center) + 2 * (size_t)n, *s = reinterpret_cast<const float *>(scale) + 2 * (size_t)n;
+        c0 = c[0]; c1 = c[1]; s0 = s[0]; s1 = s[1];
+        area = (double)__fmul_rn(__fmul_rn(s[0], 200.0f), __fmul_rn(s[1], 200.0f));
+    }
+    double *o = out + 6 * (size_t)n;
+    o[0] = c0; o[1] = c1; o[2] = s0; o[3] = s1; o[4] = area; o[5] = score ? score[n] : 1.0;
+}
+}  // namespace udp
+
+extern "C" int udp_pack_all_boxes(const void *center, const void *scale, int cs_f64, const double *score, double *all_boxes,
+                                  int N, void *stream)
+{
+    if (N < 0) return UDP_EINVAL;
+    if (N == 0) return 0;
+    if (!center || !scale || !all_boxes) return UDP_EINVAL;
+    udp::pack_all_boxes_kernel<<<(N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(center, scale, cs_f64, score, all_boxes, N);
+    UDP_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int udp_transform_preds(const void *coords, int coords_f64, const void *center,
                                    const void *scale, int cs_f64, int w, int h, double *out, int K,
                                    int N, void *stream)

@@ -403,6 +403,16 @@ def accuracy_pck(output, target, ch_stride=1, thr=0.5):
     return dict(acc=acc, avg_acc=avg, cnt=cnt, pred=pred, dists=dists)
 
 
+def pack_all_boxes(center, scale, score=None):
+    """lib/core/function.py:211-214: all_boxes rows (cx, cy, sx, sy, prod(s * 200), score) -> float64 CUDA [N,6]."""
+    center, scale, f64 = _cs(center, scale)
+    N = center.shape[0]
+    sc = _dev(score, _F64) if score is not None else None
+    out = torch.empty((N, 6), dtype=_F64, device=center.device)
+    _lib.call("udp_pack_all_boxes", _ptr(center), _ptr(scale), f64, _ptr(sc), _ptr(out), N, _stream())
+    return out
+
+
 def coco_rescore(preds, box_score, in_vis_thre):
     """the rescoring of lib/dataset/coco.py:326-339.  preds f32 CUDA [N,K,3]
     (x, y, maxval), box_score f64 [N] -> score f64 CUDA [N]."""
