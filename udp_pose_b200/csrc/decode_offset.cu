@@ -607,6 +607,8 @@ decode_offset_prune_kernel(const __grid_constant__ CUtensorMap tm_out, const __g
 
 }  // namespace udp
 
+#include "decode_offset_warp.cuh"
+
 static int decode_offset_launch(const float *out, const float *out_flipped, const float *off_out, const float *off_flipped,
                                 const int32_t *flip_perm, double kpd, const void *center,
                                 const void *scale, int cs_f64, int K, int w, int h, float *preds,
@@ -680,6 +682,38 @@ static int decode_offset_launch(const float *out, const float *out_flipped, cons
         UDP_OFF_PRUNE(48, 64, UDP_PRUNE_NT, UDP_PRUNE_MINB, UDP_PRUNE_STAGES)
         UDP_OFF_PRUNE(64, 64, UDP_PRUNE_NT, UDP_PRUNE_MINB, UDP_PRUNE_STAGES)
 #undef UDP_OFF_PRUNE
+        // the default for 64-row maps (decode_offset_warp.cuh): a warp owns a 16-column band through both passes; one CTA
+        // per SM, NTEAM teams sharing a ring of NP raw slots.  UDP_OFFSET_PIPE=1 selects the pipe kernel below instead.
+#define UDP_OFF_TEAM(WW, HH, TNT, NTEAM, NP)                                                     \
+        if (w == WW && h == HH && !pipe_on) do {                                                 \
+            using G = udp::PipeGeom<WW, HH, 7, TNT>;                                             \
+            using WG = udp::WarpGeom<WW, HH, TNT>;                                               \
+            const size_t smem = (size_t)(NP * (out_flipped ? 2 : 1) * G::BUF + NTEAM * WG::TFLOATS) * sizeof(float) + 128; \
+            void (*kern)(CUtensorMap, CUtensorMap, udp::DecodeOffsetArgs, long long) =           \
+                out_flipped ? udp::decode_offset_team_kernel<WW, HH, TNT, NTEAM, NP, true>       \
+                            : udp::decode_offset_team_kernel<WW, HH, TNT, NTEAM, NP, false>;     \
+            CUtensorMap tm_out, tm_fl;                                                           \
+            const bool tma_ok = udp::pipe_make_map(&tm_out, out, WW, HH, G::SR, 3 * maps) &&     \
+                                udp::pipe_make_map(&tm_fl, out_flipped ? out_flipped : out, WW, HH, G::SR, 3 * maps); \
+            if (!tma_ok) break;                                                                  \
+            int per_sm = 0;                                                                      \
+            int rc = udp::persistent_grid((const void *)kern, TNT * NTEAM, smem, &per_sm);       \
+            if (rc) return rc;                                                                   \
+            long long grid = (long long)per_sm * udp::sm_count();                                \
+            if (grid * NTEAM > maps) grid = (maps + NTEAM - 1) / NTEAM;                          \
+            kern<<<(unsigned)grid, TNT * NTEAM, smem, (cudaStream_t)stream>>>(tm_out, tm_fl, a, maps); \
+            UDP_LAUNCH_CHECK();                                                                  \
+            return 0;                                                                            \
+        } while (0);
+        const char *pp = getenv("UDP_OFFSET_PIPE");
+        const bool pipe_on = pp && pp[0] == '1';
+#ifndef UDP_OFF_NTEAM
+#define UDP_OFF_NTEAM 5
+#define UDP_OFF_NP 4
+#endif
+        UDP_OFF_TEAM(48, 64, 96, UDP_OFF_NTEAM, UDP_OFF_NP)
+        UDP_OFF_TEAM(64, 64, 128, 4, 3)
+#undef UDP_OFF_TEAM
 #ifndef UDP_OFF_NT
 #define UDP_OFF_NT 96
 #define UDP_OFF_MINB 4

@@ -179,20 +179,23 @@ __device__ __forceinline__ void pipe_window(const float *raw_out, const float *r
         const float4 r0 = *reinterpret_cast<const float4 *>(a0 + xc);
         const float4 r1 = *reinterpret_cast<const float4 *>(a1 + xc);
         float e[8] = {r0.x, r1.x, r0.y, r1.y, r0.z, r1.z, r0.w, r1.w};
-        if (FLIP) {
+        if (FLIP) {  // the two sums of a row pair land in a register pair, so the halving is one packed multiply
             const float4 g0 = *reinterpret_cast<const float4 *>(f0 + (W - 4 - xc));
             const float4 g1 = *reinterpret_cast<const float4 *>(f1 + (W - 4 - xc));
-            e[0] = __fmul_rn(__fadd_rn(r0.x, g0.w), 0.5f); e[1] = __fmul_rn(__fadd_rn(r1.x, g1.w), 0.5f);
-            e[2] = __fmul_rn(__fadd_rn(r0.y, g0.z), 0.5f); e[3] = __fmul_rn(__fadd_rn(r1.y, g1.z), 0.5f);
-            e[4] = __fmul_rn(__fadd_rn(r0.z, g0.y), 0.5f); e[5] = __fmul_rn(__fadd_rn(r1.z, g1.y), 0.5f);
-            e[6] = __fmul_rn(__fadd_rn(r0.w, g0.x), 0.5f); e[7] = __fmul_rn(__fadd_rn(r1.w, g1.x), 0.5f);
+            e[0] = __fadd_rn(r0.x, g0.w); e[1] = __fadd_rn(r1.x, g1.w);
+            e[2] = __fadd_rn(r0.y, g0.z); e[3] = __fadd_rn(r1.y, g1.z);
+            e[4] = __fadd_rn(r0.z, g0.y); e[5] = __fadd_rn(r1.z, g1.y);
+            e[6] = __fadd_rn(r0.w, g0.x); e[7] = __fadd_rn(r1.w, g1.x);
         }
         if (DIV255) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) e[i] = div255(e[i]);
+            for (int i = 0; i < 8; ++i) e[i] = div255(FLIP ? __fmul_rn(e[i], 0.5f) : e[i]);
         }
-        v[4 * q] = pk(e[0], e[1]); v[4 * q + 1] = pk(e[2], e[3]);
-        v[4 * q + 2] = pk(e[4], e[5]); v[4 * q + 3] = pk(e[6], e[7]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const f32x2 s = pk(e[2 * i], e[2 * i + 1]);
+            v[4 * q + i] = (FLIP && !DIV255) ? fmul2p(s, 0.5f) : s;
+        }
     }
     // reflect-101 columns at the map borders: column -1-i <- column 1+i, column W+i <- column W-2-i
     if (xs == 0) {
