@@ -102,7 +102,7 @@ __device__ __forceinline__ void warp_col_pass(const float *T, int warp, int lane
 // round trip, so 15 % of the warp samples sat in the mbarrier wait; a second pair per CTA does not fit four CTAs.
 // Pooled in one CTA, the slots go to whichever map is next: the CTA's maps k = 0, 1, 2, ... land in slot k % NP in
 // order, team t takes k = t, t + NTEAM, ...; a slot is refilled (with map k + NP) by the last warp of its team to
-// have copied its window.  NP and NTEAM are coprime (NP == NTEAM would tie each team to one slot again).
+// have copied its window.  (With NP == NTEAM that would tie each team to one slot again; the deal is then rotated.)
 // 128 registers without spills give five teams = 15 warps per SM at 64x48 (1.72 -> 1.56 ms per 16 384 persons x 17
 // maps; four teams of 168 registers: 1.78 ms, six of 96: 1.77 ms).
 // No block barrier after the prologue: a team meets on its named barrier (bar.sync team+1) only to vote.
@@ -115,9 +115,18 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
     constexpr int R = 7;
     using G = PipeGeom<W, H, R, TNT>;
     using WG = WarpGeom<W, H, TNT>;
-    constexpr int NW = G::NWARP, NBOX = NTEAM >= 5 ? 16 : 32;  // (shared memory: five teams leave room for 16-map mailboxes)
+    // Shared memory is budgeted to stay below 196 KiB per SM (ring + T buffers + mailboxes + the 1 KiB the system keeps):
+    // one step further up the carve-out ladder leaves 28 KiB of L1 instead of 60 and costs 15 % (1.52 -> 1.75 ms,
+    // measured by padding the allocation), which is also why a fifth slot or 32-map mailboxes measured slower.
+    constexpr int NW = G::NWARP, NBOX = 16;
     static_assert(TNT == 32 * NW && NW == G::XS, "whole warps, one per column band");
+    // Which team takes the CTA's k-th map, k = NP * f + s (slot s, fill f).  NP != NTEAM: team k % NTEAM (the two must be
+    // coprime, or a team would only ever see some of the slots).  NP == NTEAM: team (s + f) % NTEAM -- every group of NP
+    // maps is dealt round the teams one place further on, so team t's f-th map sits in slot (t - f) mod NP.
+    constexpr bool ROT = NP == NTEAM;
+    static_assert(ROT || (NP % NTEAM != 0 && NTEAM % NP != 0), "slots and teams");
     constexpr int B_V = 0, B_I = NW, B_MAP = 2 * NW, BOXW = 2 * NW + 1;
+    constexpr int ITEMS = (NBOX * 14 + TNT - 1) / TNT;  // vote items per thread
     constexpr int SLOT = (FLIP ? 2 : 1) * G::BUF;  // floats per ring slot: out, then flipped
     constexpr unsigned SLOT_BYTES = (FLIP ? 2u : 1u) * (unsigned)(G::SR * H * 4);
     // dynamic shared memory is only guaranteed 16-byte alignment; TMA destinations need 128
@@ -125,28 +134,26 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
     float *smem = smem_raw + ((128u - ((unsigned)__cvta_generic_to_shared(smem_raw) & 127u)) & 127u) / 4u;  // still a shared-space pointer
     __shared__ __align__(8) unsigned long long s_bars[NP];
     __shared__ unsigned s_done[NP];                       // warps that have copied their window of the slot's map
-    __shared__ int s_fill[NP];                            // which fill (k / NP) the slot's barrier has been armed for
+    __shared__ int s_fill[NP];                            // which fill the slot's barrier has been armed for
     __shared__ float s_box[NTEAM][2 * NBOX * BOXW];       // per team, two mailboxes: one fills while the other is voted on
     __shared__ float s_rows[NTEAM][NBOX * 14];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int team = warp / NW, tw = warp - team * NW, ttid = tid - team * TNT;
     float *T = smem + NP * SLOT + team * WG::TFLOATS;
     const unsigned ring0 = (unsigned)__cvta_generic_to_shared(smem), bars = (unsigned)__cvta_generic_to_shared(s_bars);
-    // this CTA's maps: m(k) = blockIdx.x + k * gridDim.x, k < KC
-    const long long KC = (maps - (long long)blockIdx.x + (long long)gridDim.x - 1) / (long long)gridDim.x;
+    // this CTA's maps: m(k) = blockIdx.x + k * gridDim.x, k < KC (maps < 2^31, checked by the launcher)
+    const int KC = (int)((maps - (long long)blockIdx.x + (long long)gridDim.x - 1) / (long long)gridDim.x);
 
-    auto issue = [&](long long k) {  // one thread: the loads of this CTA's k-th map into slot k % NP
-        const long long m = (long long)blockIdx.x + k * (long long)gridDim.x;
-        const int s = (int)(k % NP);
+    auto issue = [&](int s, int f) {  // one thread: the loads of fill f of slot s, i.e. of this CTA's map k = NP * f + s
+        const unsigned m = blockIdx.x + (unsigned)(NP * f + s) * gridDim.x;
         const unsigned bar = bars + 8u * (unsigned)s, dst = ring0 + (unsigned)s * (unsigned)(SLOT * 4);
-        *reinterpret_cast<volatile int *>(&s_fill[s]) = (int)(k / NP);
+        *reinterpret_cast<volatile int *>(&s_fill[s]) = f;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(SLOT_BYTES) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                     ::"r"(dst), "l"((unsigned long long)(uintptr_t)&tm_out), "r"(0), "r"((int)(m * 3 * H)), "r"(bar) : "memory");
+                     ::"r"(dst), "l"((unsigned long long)(uintptr_t)&tm_out), "r"(0), "r"((int)(m * 3u * H)), "r"(bar) : "memory");
         if (FLIP) {
-            const long long n = m / p.K;
-            const int kj = (int)(m - n * p.K);
-            const int row = (int)(((n * p.K + __ldg(p.flip_perm + kj)) * 3) * H);
+            const unsigned n = m / (unsigned)p.K, kj = m - n * (unsigned)p.K;
+            const int row = (int)((n * (unsigned)p.K + (unsigned)__ldg(p.flip_perm + kj)) * 3u * H);
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                          ::"r"(dst + (unsigned)(G::BUF * 4)), "l"((unsigned long long)(uintptr_t)&tm_fl), "r"(0), "r"(row), "r"(bar) : "memory");
         }
@@ -167,12 +174,25 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
         const float *boxes = s_box[team] + half * NBOX * BOXW;
         float *rows = s_rows[team];
         team_bar();  // every warp of the team has posted its candidates (and is done with the previous vote's rows)
-        for (int item = ttid; item < count * 14; item += TNT) {  // (map, channel, row) items
-            const int e = item / 14, r = item - e * 14;
-            float bv;
-            int bi;
-            const long long m = entry(boxes + e * BOXW, bv, bi);
-            rows[item] = offset_row_item(p, m, bv, bi, r / 7, r - (r / 7) * 7);
+        // (map, channel, row) items: unrolled, so that the scattered global loads of all of a thread's items are in
+        // flight together (rolled, the ITEMS round trips to HBM come one after the other)
+        float res[ITEMS];
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int item = ttid + it * TNT;
+            res[it] = 0.0f;
+            if (item < count * 14) {
+                const int e = item / 14, r = item - e * 14;
+                float bv;
+                int bi;
+                const long long m = entry(boxes + e * BOXW, bv, bi);
+                res[it] = offset_row_item(p, m, bv, bi, r / 7, r - (r / 7) * 7);
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int item = ttid + it * TNT;
+            if (item < count * 14) rows[item] = res[it];
         }
         team_bar();
         if (tw == 0 && lane < count) {  // one map per lane; the other warps are already filling the other mailbox
@@ -194,19 +214,19 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
     }
     __syncthreads();
     if (tid == 0)
-        for (int k = 0; k < NP && k < KC; ++k) issue(k);
+        for (int s = 0; s < NP && s < KC; ++s) issue(s, 0);
 
+    // this team's sequence of (slot, fill): see ROT above
+    int s = ROT ? team : team % NP, f = ROT ? 0 : team / NP;
     int slot_n = 0, half = 0;
-    for (long long k = team; k < KC; k += NTEAM) {
-        const long long map = (long long)blockIdx.x + k * (long long)gridDim.x;
+    while (NP * f + s < KC) {
+        const int k = NP * f + s;
         if (slot_n == NBOX) { flush(NBOX, half); slot_n = 0; half ^= 1; }
-        const int s = (int)(k % NP);
         // A parity wait can only tell "this phase" from "the one before": a team that is more than a fill ahead of the team
         // that frees its next slot (the slot's barrier still in the phase before last) would be let through.  So first
         // see the slot armed for OUR fill (a plain flag written by the issuer before it arms the barrier).
-        const int fill = (int)(k / NP);
-        while (*reinterpret_cast<volatile int *>(&s_fill[s]) != fill) {}
-        mbar_wait(bars + 8u * (unsigned)s, (unsigned)(fill & 1));  // per-thread wait on the slot's fill
+        while (*reinterpret_cast<volatile int *>(&s_fill[s]) != f) {}
+        mbar_wait(bars + 8u * (unsigned)s, (unsigned)(f & 1));  // per-thread wait on the slot's fill
         const float *bufP = smem + s * SLOT, *bufQ = bufP + G::BUF;
 
         f32x2 v[G::NCOL];
@@ -217,7 +237,7 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
         if (lane == 0) {
             if (atomicAdd(&s_done[s], 1u) == (unsigned)(NW - 1)) {
                 s_done[s] = 0u;
-                if (k + NP < KC) issue(k + NP);
+                if (k + NP < KC) issue(s, f + 1);
             }
         }
         const f32x2 tsum = warp_row_filter<W, H, TNT>(v, T, lane, tw);
@@ -258,8 +278,16 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
         }
         float *box = s_box[team] + (half * NBOX + slot_n) * BOXW;
         if (lane == 0) { box[B_V + tw] = bv; box[B_I + tw] = __int_as_float(bi); }
-        if (ttid == 0) box[B_MAP] = __int_as_float((int)map);
+        if (ttid == 0) box[B_MAP] = __int_as_float((int)(blockIdx.x + (unsigned)k * gridDim.x));
         ++slot_n;
+        if (ROT) {  // next group, one slot back
+            s = s == 0 ? NP - 1 : s - 1;
+            ++f;
+        } else {  // k += NTEAM
+            s += NTEAM % NP;
+            f += NTEAM / NP;
+            if (s >= NP) { s -= NP; ++f; }
+        }
     }
     if (slot_n) flush(slot_n, half);
 }
