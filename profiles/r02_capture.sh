@@ -22,7 +22,7 @@ cap() { # name kernel-regex skip command...
 B="python bench.py --steps 2 --warmup 3 --no-cpu --no-e2e --no-configs --no-sweep"
 cap crop_tma warp_affine_u8_tma_kernel 3 $B --no-fused
 cap encode_offset encode_offset_kernel 3 $B --no-fused
-cap decode_offset decode_offset_pipe_kernel 3 $B --no-fused
+cap decode_offset decode_offset_team_kernel 3 $B --no-fused
 cap crop_f32 "warp_affine_u8_tma_kernel.*CropOutF32" 1 $B
 cap pck_dist pck_dist_kernel 1 $B
 cap decode_quarter decode_quarter_kernel 1 $B

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["affine.cu", "crop.cu", "encode.cu", "decode.cu", "decode_offset.cu", "evaluate.cu", "nms.cu", "legacy.cu", "aid.cu"]
-HEADERS = ["common.cuh", "blur.cuh", "blur_fast.cuh", "decode_pipe.cuh", "tma_host.cuh", os.path.join("..", "..", "include", "udp_codec.h")]
+HEADERS = ["common.cuh", "blur.cuh", "blur_fast.cuh", "decode_pipe.cuh", "decode_offset_prune.cuh", "decode_offset_warp.cuh", "tma_host.cuh", os.path.join("..", "..", "include", "udp_codec.h")]
 OUT = os.path.join(HERE, "libudp_codec.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
