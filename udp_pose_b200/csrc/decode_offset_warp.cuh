@@ -117,17 +117,23 @@ decode_offset_team_kernel(const __grid_constant__ CUtensorMap tm_out, const __gr
     using WG = WarpGeom<W, H, TNT>;
     // Shared memory is budgeted to stay below 196 KiB per SM (ring + T buffers + mailboxes + the 1 KiB the system keeps):
     // one step further up the carve-out ladder leaves 28 KiB of L1 instead of 60 and costs 15 % (1.52 -> 1.75 ms,
-    // measured by padding the allocation), which is also why a fifth slot or 32-map mailboxes measured slower.
-    constexpr int NW = G::NWARP, NBOX = 16;
+    // measured by padding the allocation) -- the vote's scattered loads live on L1 hits.  That is why a fifth slot
+    // measured slower; the mailboxes take what is left (24 maps at 64x48 with the mirrored partner: 2 % over 16).
+    constexpr int NW = G::NWARP;
+    constexpr int B_V = 0, B_I = NW, B_MAP = 2 * NW, BOXW = 2 * NW + 1;
+    constexpr int SLOT = (FLIP ? 2 : 1) * G::BUF;  // floats per ring slot: out, then flipped
+    constexpr int DYN_BYTES = (NP * SLOT + NTEAM * WG::TFLOATS) * 4 + 128;
+    constexpr int BOX_BYTES = NTEAM * (2 * BOXW + 14) * 4;  // one more map in every team's two mailboxes and row buffer
+    constexpr int ROOM = (196 * 1024 - 1024 - DYN_BYTES - 256) / BOX_BYTES;
+    constexpr int NBOX = ROOM >= 32 ? 32 : (ROOM & ~3);  // (one map per lane in the vote's last step: at most 32)
+    static_assert(NBOX >= 8, "shared memory budget");
     static_assert(TNT == 32 * NW && NW == G::XS, "whole warps, one per column band");
     // Which team takes the CTA's k-th map, k = NP * f + s (slot s, fill f).  NP != NTEAM: team k % NTEAM (the two must be
     // coprime, or a team would only ever see some of the slots).  NP == NTEAM: team (s + f) % NTEAM -- every group of NP
     // maps is dealt round the teams one place further on, so team t's f-th map sits in slot (t - f) mod NP.
     constexpr bool ROT = NP == NTEAM;
     static_assert(ROT || (NP % NTEAM != 0 && NTEAM % NP != 0), "slots and teams");
-    constexpr int B_V = 0, B_I = NW, B_MAP = 2 * NW, BOXW = 2 * NW + 1;
     constexpr int ITEMS = (NBOX * 14 + TNT - 1) / TNT;  // vote items per thread
-    constexpr int SLOT = (FLIP ? 2 : 1) * G::BUF;  // floats per ring slot: out, then flipped
     constexpr unsigned SLOT_BYTES = (FLIP ? 2u : 1u) * (unsigned)(G::SR * H * 4);
     // dynamic shared memory is only guaranteed 16-byte alignment; TMA destinations need 128
     extern __shared__ __align__(16) float smem_raw[];
