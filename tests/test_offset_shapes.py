@@ -102,3 +102,47 @@ def test_gpu_offset_team_and_pipe_kernels_agree(cuda, monkeypatch):
     b = cuda.decode(cfg, out, fl, c, s)
     for k in ("idx", "maxvals", "preds", "preds_in"):
         assert parity.same_bits(a[k], b[k]), k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(48, 64), (64, 64)])
+def test_gpu_offset_team_kernel_sizes_and_repeats(shape):
+    """Batch sizes around the team kernel's corners (fewer maps than teams, a partial last group, one map more or less
+    than CTAs x teams, several ring revolutions), each decoded three times: the hand-off between teams is dynamic, the
+    result must not be.  Reference: the barrier-per-map kernel (UDP_OFFSET_PIPE=1); NaN payloads aside, same bits."""
+    import os
+    import torch
+    from udp_pose_b200 import device_api as D
+    w, h = shape
+    cfg = _cfg(w, h)
+    old = os.environ.get("UDP_OFFSET_PIPE")
+    try:
+        for N in (1, 3, 17, 44, 45, 175, 871):
+            rng = np.random.default_rng(N * 7 + w)
+            out, fl = synth.heatmaps(cfg, N, rng)
+            c, s, _ = synth.boxes(cfg, N, rng)
+            if N >= 17:
+                out[N // 2, 3 * 2, h // 2, w // 3] = np.nan
+                out[N // 3, 0, 0, 0] = np.inf
+                fl[N - 1, 3 * 5, h - 1, w - 1] = -np.inf
+            o, f = torch.from_numpy(out).cuda(), torch.from_numpy(fl).cuda()
+            ct, st = torch.from_numpy(c).cuda(), torch.from_numpy(s).cuda()
+            for flip in (True, False):
+                os.environ["UDP_OFFSET_PIPE"] = "1"
+                ref = {k: v.clone() for k, v in D.decode_batch(cfg, o, f if flip else None, ct, st, want_packed=True).items() if v is not None}
+                os.environ["UDP_OFFSET_PIPE"] = "0"
+                for _ in range(3):
+                    r = D.decode_batch(cfg, o, f if flip else None, ct, st, want_packed=True)
+                    for k, a in ref.items():
+                        b = r[k]
+                        if a.dtype == torch.float32:
+                            na, nb = torch.isnan(a), torch.isnan(b)
+                            assert torch.equal(na, nb), (N, flip, k)
+                            assert torch.equal(a[~na].view(torch.int32), b[~nb].view(torch.int32)), (N, flip, k)
+                        else:
+                            assert torch.equal(a, b), (N, flip, k)
+    finally:
+        if old is None:
+            os.environ.pop("UDP_OFFSET_PIPE", None)
+        else:
+            os.environ["UDP_OFFSET_PIPE"] = old
